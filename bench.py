@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native dense-stereo hot path.
+
+Metric (BASELINE.json): Gpix-disp/s = H*W*D / s for SSD + SGM + WTA at 1920x1080, D=128.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--frames F] [--impl b200|reference]
+
+A *step* is one pass of the hot path (SSD k=7 -> Semiglobal P1=.1 P2=.2 -> WTA, through the
+reference-shaped Python API over the C ABI) over a batch of F distinct synthetic 1080p
+stereo pairs per GPU.  Frames are sharded across ranks with no collective (weak scaling).
+One JSON line is printed by rank 0:
+  value     device-resident throughput (inputs already in HBM), CUDA events, max over ranks
+  e2e       same metric with HOST buffers: pinned H2D of both images and D2H of the
+            disparity map inside the timed region, every frame
+  roofline  dominant stage (SGM) against the measured HBM copy bandwidth
+  cpu_baseline  the unmodified reference CPU ops (oracle/_ref) on a bounded sample
+`--impl reference` times the reference's own CPU implementation (rank 0 only).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "stereo-matching_b200"))
+
+H, W, D = 1080, 1920, 128
+KERNEL_SIZE, P1, P2 = 7, 0.1, 0.2
+METRIC = "Gpix-disp/s (H*W*D) SSD+SGM+WTA 1080p D=128"
+# algorithmic (compulsory) bytes per pixel-disparity, SURVEY.md 8(d) / DESIGN.md
+ALGO_BYTES = {"ssd": 4.0 + 8.0 / D, "sgm": 8.0 + 4.0 / D, "wta": 4.0 + 4.0 / D}
+
+
+def measured_peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if (t0 is None or t0 <= t <= t1)] or [r for _, r in self.rows]
+        mhz, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                mhz.append(float(r[1]))
+                mx = float(r[2])
+                for n, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        mhz.sort()
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(mhz)}
+
+
+def make_frames(n_frames: int, first_seed: int):
+    from oracle import synth
+    return [synth.random_dot_pair(H, W, D, seed=first_seed + f, scale="raw")[:2]
+            for f in range(n_frames)]
+
+
+# ---------------------------------------------------------------------------------------
+# reference CPU arm / cpu_baseline
+# ---------------------------------------------------------------------------------------
+def cpu_reference_sample(rows: int, seed: int = 1000):
+    """SSD+SGM+WTA of the reference's own CPU ops on a `rows` x 1920 x 128 crop of the
+    workload; returns (seconds, pix-disp, kind, cores)."""
+    import numpy as np
+    from oracle import ref_ops, oracle as O, synth
+    left, right, _ = synth.random_dot_pair(rows, W, D, seed=seed, scale="raw")
+    if ref_ops.available():
+        import torch
+        torch.set_num_threads(1)  # the reference CPU path is single-threaded as shipped
+        ops, kind = ref_ops, "reference"
+    else:
+        ops, kind = None, "port"
+    t0 = time.perf_counter()
+    if ops is not None:
+        cost = ops.ssd(left, right, D, KERNEL_SIZE)
+        agg = ops.sgm(cost, left, P1, P2)
+        disp = ops.wta(agg)
+    else:
+        cost = O.ssd(left, right, D, KERNEL_SIZE)
+        agg = O.sgm(cost, left, P1, P2)
+        disp = O.wta(agg)
+    dt = time.perf_counter() - t0
+    assert disp.shape == (rows, W) and np.isfinite(agg[:, D:, :]).all()
+    return dt, rows * W * D, kind, 1
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    rows = args.ref_rows
+    for _ in range(args.warmup):
+        cpu_reference_sample(rows)
+    t_total, px_total, kind, cores = 0.0, 0, "port", 1
+    for s in range(args.steps):
+        dt, px, kind, cores = cpu_reference_sample(rows, seed=1000 + s)
+        t_total += dt
+        px_total += px
+    value = px_total / t_total / 1e9
+    sample = f"{rows}x{W}x{D} crop (rows of the 1080p workload) per step, SSD k=7 + SGM + WTA"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Gpix-disp/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * t_total / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "1920x1080 D=128 SSD(k=7)+SGM(P1=.1,P2=.2)+WTA random-dot stereogram",
+                   "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "Gpix-disp/s", "cores": cores, "kind": kind,
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "Gpix-disp/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    import stereomatch
+    from stereomatch import _cstereomatch as C
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    F = args.frames
+    # frame f of rank r: seed 1000 + r*F + f (frame-sharded batch, no collective)
+    host = make_frames(F, 1000 + rank * F)
+    pinned = [(torch.from_numpy(l).pin_memory(), torch.from_numpy(r).pin_memory()) for l, r in host]
+    dev_frames = [(l.to(dev), r.to(dev)) for l, r in pinned]
+    out_host = [torch.empty(H, W, dtype=torch.int32).pin_memory() for _ in range(F)]
+
+    ssd = stereomatch.cost.SSD(D, KERNEL_SIZE)
+    sgm = stereomatch.aggregation.Semiglobal(P1, P2)
+    wta = stereomatch.disparity_reduce.WinnerTakesAll()
+    pipe = stereomatch.Pipeline(ssd, wta, sgm)
+
+    def step_resident():
+        for l, r in dev_frames:
+            pipe.estimate(l, r)
+
+    def step_e2e():
+        for (l, r), o in zip(pinned, out_host):
+            disp = pipe.estimate(l.to(dev, non_blocking=True), r.to(dev, non_blocking=True))
+            o.copy_(disp, non_blocking=True)
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        t1 = time.perf_counter()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), t0, t1
+
+    for _ in range(args.warmup):
+        step_resident()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    launches0 = C.launch_count()
+    ms, t0, t1 = timed(step_resident, args.steps)
+    launches = C.launch_count() - launches0
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    ms_e2e, _, _ = timed(step_e2e, args.steps)
+
+    # per-stage device times (CUDA events on the launching stream), for the roofline
+    stage_ms = {"ssd": 0.0, "sgm": 0.0, "wta": 0.0}
+    reps = max(3, min(args.steps, 10))
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    l, r = dev_frames[0]
+    for rep in range(reps):
+        l, r = dev_frames[rep % F]
+        ev[0].record()
+        cost = ssd(l, r, cost_volume=pipe._cost_volume)
+        ev[1].record()
+        agg = sgm(cost, l, pipe._aggregation_volume)
+        ev[2].record()
+        wta(agg, pipe._disparity_image)
+        ev[3].record()
+        torch.cuda.synchronize()
+        stage_ms["ssd"] += ev[0].elapsed_time(ev[1]) / reps
+        stage_ms["sgm"] += ev[1].elapsed_time(ev[2]) / reps
+        stage_ms["wta"] += ev[2].elapsed_time(ev[3]) / reps
+    sgm_launches0 = C.launch_count()
+    sgm(cost, l, pipe._aggregation_volume)
+    sgm_launches = C.launch_count() - sgm_launches0
+    torch.cuda.synchronize()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    N = H * W * D
+    total_px = N * F * world * args.steps
+    value = total_px / (ms * 1e-3) / 1e9
+    e2e = total_px / (ms_e2e * 1e-3) / 1e9
+    peak, peak_kind = measured_peak()
+    dom = max(stage_ms, key=stage_ms.get)
+    achieved = ALGO_BYTES[dom] * N / (stage_ms[dom] * 1e-3) / 1e9
+    traffic = None
+    tp = ROOT / "profiles" / "traffic.json"
+    if tp.exists():
+        try:
+            traffic = json.loads(tp.read_text()).get(dom)
+        except Exception:
+            traffic = None
+    stages = {k: {"ms": round(v, 4), "algo_GBs": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9, 1),
+                  "frac": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9 / peak, 4)}
+              for k, v in stage_ms.items()}
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline:
+        dt, px, kind, cores = cpu_reference_sample(args.cpu_rows)
+        cpu_baseline = {"value": px / dt / 1e9, "unit": "Gpix-disp/s", "cores": cores, "kind": kind,
+                        "sample": f"{args.cpu_rows}x{W}x{D} crop of frame 0, SSD+SGM+WTA, "
+                                  f"{dt:.1f} s on 1 of {os.cpu_count()} host cores"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "Gpix-disp/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "ms_per_frame": ms / args.steps / F, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "1920x1080 D=128 SSD(k=7)+SGM(P1=.1,P2=.2, reference path set)+WTA, "
+                               "random-dot stereograms", "frames_per_gpu_per_step": F,
+                   "sharding": f"frame-sharded x{world}, no collective",
+                   "l2": "working set per frame (2 x 1.06 GB volumes) exceeds the 126 MB L2"},
+        "e2e": {"value": e2e, "unit": "Gpix-disp/s",
+                "h2d_bytes_per_step": 2 * H * W * 4 * F, "d2h_bytes_per_step": H * W * 4 * F,
+                "ms_per_frame": ms_e2e / args.steps / F},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": f"{dom} stage ({sgm_launches} launches)" if dom == "sgm" else dom,
+                     "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic},
+        "stages": stages,
+        "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--frames", type=int, default=4, help="stereo pairs per GPU per step")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-rows", type=int, default=160, help="rows of the cpu_baseline crop")
+    ap.add_argument("--ref-rows", type=int, default=64, help="rows per step of --impl reference")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,105 @@
+/*
+ * stm_abi.h -- C ABI of libstm_b200.so, the B200-native (sm_100a) dense-stereo hot path.
+ *
+ * This is the drop-in boundary for the reference's pybind11 module
+ * `stereomatch._cstereomatch` (reference src/_cstereomatch.cpp:10-17).  Each entry point
+ * below replaces one static method of that module; the reference-side binding a
+ * maintainer would add is shown in INTEGRATION.md, and
+ * stereo-matching_b200/stereomatch/_cstereomatch.py is that binding (ctypes).
+ *
+ * Conventions
+ *  - `*_f32` entry points take DEVICE pointers and enqueue on `stream` (a cudaStream_t
+ *    passed as void*; NULL = legacy default stream) of the CURRENT device; they never
+ *    allocate, never synchronise the device, and are CUDA-graph capturable.
+ *  - `*_host_f32` entry points take HOST pointers, do the host<->device copies themselves
+ *    (synchronous; scratch device memory is cached per thread) and return when the
+ *    result is in the host buffer.
+ *  - Volumes are contiguous row-major [H, W, D] float32 with D innermost (element (y,x,d)
+ *    at (y*W + x)*D + d), images [H, W] float32, disparity maps [H, W] int32 -- the
+ *    reference's layout.
+ *  - Return value: STM_OK (0) or a negative status; stm_last_error() returns a
+ *    thread-local message for the last failure (the binding raises RuntimeError with it,
+ *    mirroring the reference's C++ exceptions, include/stereomatch/check.hpp:12-37).
+ *  - There is NO CPU fallback: without a CUDA device every compute call fails with
+ *    STM_ECUDA.
+ */
+#ifndef STM_ABI_H_
+#define STM_ABI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STM_OK 0
+#define STM_EINVAL (-1)       /* bad argument (shape, null pointer, alignment) */
+#define STM_ECUDA (-2)        /* CUDA runtime error; message holds cudaGetErrorString */
+#define STM_EUNSUPPORTED (-3) /* valid request this build does not implement */
+
+/* flags of stm_sgm_f32 */
+#define STM_SGM_MIN_ALL_D 1u /* min_k over all D (reference CUDA kernel, src/semiglobal_gpu.cu:70-81)
+                                instead of k in [0, D-2] (compiled CPU reference,
+                                src/bordered_buffer.hpp:26-27) */
+#define STM_SGM_OVERWRITE 2u /* out = sum (skip the caller's zero fill) instead of out += sum */
+
+/* flags of stm_dp_f32 */
+#define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68);
+                               requires D <= H <= W and a zeroed path volume */
+
+/* Library / build identification, e.g. "stm_b200 0.1 sm_100a". */
+const char *stm_version(void);
+const char *stm_last_error(void);
+
+/* Replaces CostOps.compute_ssd(left, right, cost_volume, kernel_size)
+ * (reference src/cost.cpp:6-9 -> CostOps::ComputeSSD, src/ssd.cu:64-81).
+ * cost[y,x,d] = sum over rows [max(y-k,0), min(y+k,H)) x cols [max(x-k,d), min(x+k,W))
+ * of (left[r,c] - right[r,c-d])^2 for d <= x, +inf for d > x. */
+int stm_ssd_f32(const float *left, const float *right, float *cost, int H, int W, int D,
+                int kernel_size, void *stream);
+
+/* Replaces CostOps.compute_birchfield(left, right, cost_volume, kernel_size)
+ * (reference src/cost.cpp:14 -> CostOps::ComputeBirchfield, src/birchfield_cost.cu:153-181;
+ * kernel size is the reference's template constant 4).  Semantics of the reference CUDA
+ * functor (zero-padded scanlines); entries d > x, which the reference leaves unwritten,
+ * are set to +inf. */
+int stm_birchfield_f32(const float *left, const float *right, float *cost, int H, int W,
+                       int D, void *stream);
+
+/* Replaces AggregationOps.run_semiglobal(cost, left_image, p1, p2, out)
+ * (reference src/aggregation.cpp:6 -> AggregationOps::RunSemiglobal, src/semiglobal.cpp:167-197).
+ * Aggregates over the reference path set (8 directions, including its stored-end quirk)
+ * and ACCUMULATES into `out` unless STM_SGM_OVERWRITE.  `workspace` must hold
+ * stm_sgm_workspace_bytes(H, W, D) bytes of device memory (may be NULL if that is 0). */
+size_t stm_sgm_workspace_bytes(int H, int W, int D);
+int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, int D,
+                float penalty1, float penalty2, unsigned flags, void *workspace,
+                size_t workspace_bytes, void *stream);
+
+/* Replaces DisparityReduceOps.run_winners_take_all(cost, disparity)
+ * (reference src/disparity_reduce.cpp:6-9 -> RunWinnersTakeAll, src/winners_take_all.cu:89-114).
+ * CPU rule: first (lowest-d) minimum, all-inf -> 0, NaN never wins.  Any D >= 1. */
+int stm_wta_f32(const float *cost, int32_t *disparity, int H, int W, int D, void *stream);
+
+/* Replaces DisparityReduceOps.run_dynamic_programming(cost, path, row_final, disparity)
+ * (reference src/disparity_reduce.cpp:6-9 -> RunDynamicProgramming,
+ * src/dynamic_programming.cu:184-225).  path: int8 [H,W,D]; row_final: float32 [H,D]. */
+int stm_dp_f32(const float *cost, int8_t *path, float *row_final, int32_t *disparity, int H,
+               int W, int D, unsigned flags, void *stream);
+
+/* Host-buffer form of Pipeline.estimate (reference stereomatch/pipeline.py:69-94):
+ * cost (0 = SSD, 1 = Birchfield) -> optional SGM (use_sgm) -> reducer (0 = WTA, 1 = DP).
+ * left/right/disparity are HOST pointers; copies are inside the call. */
+int stm_pipeline_host_f32(const float *left, const float *right, int32_t *disparity, int H,
+                          int W, int D, int cost_kind, int kernel_size, int use_sgm,
+                          float penalty1, float penalty2, unsigned sgm_flags, int reducer,
+                          unsigned dp_flags);
+
+/* Number of kernel launches the library has enqueued in this process (bench "gpu_launches"). */
+unsigned long long stm_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STM_ABI_H_ */

@@ -1,0 +1,19 @@
+// cost.cu -- dispatch of the cost-volume builders.
+#include "stm_common.cuh"
+
+namespace stm {
+
+int launch_ssd_generic(const float *, const float *, float *, int, int, int, int, cudaStream_t);
+int launch_birchfield_generic(const float *, const float *, float *, int, int, int, cudaStream_t);
+
+int launch_ssd(const float *left, const float *right, float *cost, int H, int W, int D, int k,
+               cudaStream_t stream) {
+  return launch_ssd_generic(left, right, cost, H, W, D, k, stream);
+}
+
+int launch_birchfield(const float *left, const float *right, float *cost, int H, int W, int D,
+                      cudaStream_t stream) {
+  return launch_birchfield_generic(left, right, cost, H, W, D, stream);
+}
+
+}  // namespace stm

@@ -1,0 +1,201 @@
+// dp.cu -- scanline dynamic-programming disparity reducer.
+//
+// Replaces DisparityReduceOps::RunDynamicProgramming (reference
+// src/dynamic_programming.cu:184-225): forward min-plus pass with 3-neighbour transitions
+// and int8 back-pointers, first-min of the final row costs (torch::argmin, :207), and the
+// per-row backtrack (ReducePathsKernel, :166-181).
+//
+// Default mode = the reference CUDA functor (ExpandPathsKernelCUDA, :83-130) with its
+// shared-memory race resolved as read-before-write: all three neighbours come from the
+// previous column.  One warp per image row, the D running costs spread over the lanes
+// (lanevec.cuh), neighbours by shuffle, back-pointers stored as packed bytes; forward
+// pass, argmin and backtrack are fused in one kernel so the row's path bytes are re-read
+// while still L2-resident.
+//
+// STM_DP_CPU_EXACT = the reference CPU functor (ExpandPathsKernelCPU, :24-68) literally,
+// including its transposed column-0 read, its in-place (Gauss-Seidel) scan over d and the
+// path[d][row][0] = 0 clobber; serial in d by construction, kept for literal parity only.
+#include "lanevec.cuh"
+#include "sgm_paths.cuh"
+
+namespace stm {
+
+template <int NV, int VW>
+__global__ void __launch_bounds__(128)
+dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
+              float *__restrict__ row_final, int32_t *__restrict__ disp, int H, int W, int D) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= H) return;
+  const size_t row_off = (size_t)row * W;
+
+  LaneVec<NV, VW> acc, c_next;
+  lv_load<NV, VW, true>(acc, cost + row_off * D, lane, D);
+  // column 0 of the path volume: zero (never read by the backtrack)
+  {
+    int8_t *p0 = path + row_off * D;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int j = 0; j < VW; ++j) {
+        const int d = lv_d<NV, VW>(lane, k, j);
+        if (d < D) p0[d] = 0;
+      }
+  }
+  if (W > 1) lv_load<NV, VW, true>(c_next, cost + (row_off + 1) * D, lane, D);
+
+  for (int col = 1; col < W; ++col) {
+    LaneVec<NV, VW> cur = c_next;
+    if (col + 1 < W) lv_load<NV, VW, true>(c_next, cost + (row_off + col + 1) * D, lane, D);
+    LaneVec<NV, VW> lo, hi;
+    lv_neighbours<NV, VW>(acc, lo, hi, lane);
+    int8_t *pp = path + (row_off + col) * D;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      int8_t dirs[VW];
+#pragma unroll
+      for (int j = 0; j < VW; ++j) {
+        const float c1 = lo.v[k][j], c2 = acc.v[k][j], c3 = hi.v[k][j];
+        float m;
+        int8_t dir;
+        if (c1 < c2 && c1 < c3) { m = c1; dir = -1; }
+        else if (c2 < c3) { m = c2; dir = 0; }
+        else { m = c3; dir = 1; }
+        dirs[j] = dir;
+        acc.v[k][j] = __fadd_rn(cur.v[k][j], m);
+      }
+      const int d0 = lv_d<NV, VW>(lane, k, 0);
+      if constexpr (VW == 4) {
+        *reinterpret_cast<char4 *>(pp + d0) = make_char4(dirs[0], dirs[1], dirs[2], dirs[3]);
+      } else if constexpr (VW == 2) {
+        *reinterpret_cast<char2 *>(pp + d0) = make_char2(dirs[0], dirs[1]);
+      } else {
+        if (d0 < D) pp[d0] = dirs[0];
+      }
+    }
+  }
+
+  lv_store<NV, VW, false>(acc, row_final + (size_t)row * D, lane, D);
+
+  // first minimum of the final costs (torch::argmin semantics)
+  float best = CUDART_INF_F;
+  int idx = 0x7fffffff;
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int j = 0; j < VW; ++j) {
+      const int d = lv_d<NV, VW>(lane, k, j);
+      const float v = acc.v[k][j];
+      if (d < D && (v < best || (v == best && d < idx))) { best = v; idx = d; }
+    }
+#pragma unroll
+  for (int m = 1; m < 32; m <<= 1) {
+    const float ov = __shfl_xor_sync(FULL, best, m);
+    const int oi = __shfl_xor_sync(FULL, idx, m);
+    if (ov < best || (ov == best && oi < idx)) { best = ov; idx = oi; }
+  }
+  int e = idx == 0x7fffffff ? 0 : idx;
+
+  // backtrack (one lane; the row's path bytes were just written by this warp)
+  __syncwarp();
+  if (lane == 0) {
+    int32_t *drow = disp + row_off;
+    drow[W - 1] = e;
+    const int8_t *prow = path + row_off * D;
+    for (int col = W - 2; col >= 0; --col) {
+      const int step = __ldcg(reinterpret_cast<const signed char *>(prow + (size_t)col * D + e));
+      e += step;
+      e = e < 0 ? 0 : (e > D - 1 ? D - 1 : e);
+      drow[col] = e;
+    }
+  }
+}
+
+// ---- literal CPU-functor variant -----------------------------------------------------
+__global__ void dp_cpu_exact_forward_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
+                                            float *row_final, int H, int W, int D) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= H) return;
+  float *prev = row_final + (size_t)row * D;  // running costs live in row_final[row]
+  for (int d = 0; d < D; ++d) prev[d] = cost[((size_t)d * W + row) * D];  // cost[d][row][0] (sic)
+  for (int col = 1; col < W; ++col) {
+    const float *c = cost + ((size_t)row * W + col) * D;
+    int8_t *p = path + ((size_t)row * W + col) * D;
+    float left = CUDART_INF_F;  // prev[d-1], already updated for this column
+    for (int d = 0; d < D; ++d) {
+      const float c1 = left, c2 = prev[d], c3 = d < D - 1 ? prev[d + 1] : CUDART_INF_F;
+      float m;
+      int8_t dir;
+      if (c1 < c2 && c1 < c3) { m = c1; dir = -1; }
+      else if (c2 < c3) { m = c2; dir = 0; }
+      else { m = c3; dir = 1; }
+      p[d] = dir;
+      left = __fadd_rn(c[d], m);
+      prev[d] = left;
+    }
+  }
+}
+
+// Net effect of the reference's `path[disp][row][0] = 0` executed in increasing row
+// order (dynamic_programming.cu:38): path[y][x][0] = 0 for y < D, y < x < H, and column 0.
+__global__ void dp_cpu_exact_clobber_kernel(int8_t *__restrict__ path, int H, int W, int D) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;  // = reference `row`
+  const int y = blockIdx.y;                             // = reference `disp`
+  if (x >= H || y >= D) return;
+  if (x == 0 || y < x) path[((size_t)y * W + x) * D] = 0;
+}
+
+__global__ void dp_backtrack_kernel(const int8_t *__restrict__ path, const float *__restrict__ row_final,
+                                    int32_t *__restrict__ disp, int H, int W, int D) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= H) return;
+  const float *f = row_final + (size_t)row * D;
+  int e = 0;
+  for (int d = 1; d < D; ++d)
+    if (f[d] < f[e]) e = d;
+  int32_t *drow = disp + (size_t)row * W;
+  drow[W - 1] = e;
+  const int8_t *prow = path + (size_t)row * W * D;
+  for (int col = W - 2; col >= 0; --col) {
+    e += prow[(size_t)col * D + e];
+    e = e < 0 ? 0 : (e > D - 1 ? D - 1 : e);
+    drow[col] = e;
+  }
+}
+
+template <int NV, int VW>
+static int run_dp(const float *cost, int8_t *path, float *row_final, int32_t *disp, int H, int W,
+                  int D, cudaStream_t stream) {
+  const int warps = 4;
+  dp_row_kernel<NV, VW><<<(H + warps - 1) / warps, warps * 32, 0, stream>>>(cost, path, row_final,
+                                                                           disp, H, W, D);
+  return check_launch("dp_row_kernel");
+}
+
+int launch_dp(const float *cost, int8_t *path, float *row_final, int32_t *disp, int H, int W,
+              int D, unsigned flags, cudaStream_t stream) {
+  if (flags & STM_DP_CPU_EXACT) {
+    if (D > H || H > W)
+      return fail(STM_EINVAL, "dp: STM_DP_CPU_EXACT requires D <= H <= W (the reference CPU "
+                  "functor reads cost[d][row][0]); got H=%d W=%d D=%d", H, W, D);
+    dp_cpu_exact_forward_kernel<<<(H + 63) / 64, 64, 0, stream>>>(cost, path, row_final, H, W, D);
+    int rc = check_launch("dp_cpu_exact_forward_kernel");
+    if (rc) return rc;
+    dp_cpu_exact_clobber_kernel<<<dim3((H + 127) / 128, D), 128, 0, stream>>>(path, H, W, D);
+    rc = check_launch("dp_cpu_exact_clobber_kernel");
+    if (rc) return rc;
+    dp_backtrack_kernel<<<(H + 63) / 64, 64, 0, stream>>>(path, row_final, disp, H, W, D);
+    return check_launch("dp_backtrack_kernel");
+  }
+  const LaneMap m = pick_lane_map(D);
+#define STM_DP_CASE(NV_, VW_) \
+  if (m.NV == NV_ && m.VW == VW_) return run_dp<NV_, VW_>(cost, path, row_final, disp, H, W, D, stream);
+  STM_DP_CASE(1, 4) STM_DP_CASE(2, 4) STM_DP_CASE(3, 4) STM_DP_CASE(4, 4)
+  STM_DP_CASE(1, 2) STM_DP_CASE(3, 2) STM_DP_CASE(5, 2) STM_DP_CASE(7, 2)
+  STM_DP_CASE(1, 1) STM_DP_CASE(2, 1) STM_DP_CASE(3, 1) STM_DP_CASE(4, 1)
+  STM_DP_CASE(5, 1) STM_DP_CASE(6, 1) STM_DP_CASE(7, 1) STM_DP_CASE(8, 1)
+#undef STM_DP_CASE
+  return fail(STM_EUNSUPPORTED, "dp: D=%d not supported", D);
+}
+
+}  // namespace stm

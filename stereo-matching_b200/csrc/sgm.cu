@@ -1,0 +1,238 @@
+// sgm.cu -- semiglobal path aggregation over the reference path set.
+//
+// Replaces AggregationOps::RunSemiglobal (reference src/semiglobal.cpp:167-197; recurrence
+// SGMCostOperator::operator(), :116-159; CUDA variant src/semiglobal_gpu.cu:43-106).
+//
+// Per directed path p0..p(n-1):  L0 = C[p0];  for i >= 1
+//     m   = min_{k in K} L(i-1)[k]              K = [0, D-2] (CPU reference) or [0, D-1]
+//     P2' = max(P1, P2 / |I[pi] - I[p(i-1)]|)   std::max semantics (x/0 = inf, 0/0 -> P1)
+//     Li[d] = (C[pi,d] + min(L[d], L[d-1]+P1, L[d+1]+P1, m+P2')) - m
+//   out[pi,:] += Li for every i including 0.
+//
+// Round-1 kernel: one warp per directed path, one launch per direction in the
+// reference's accumulation order (-> <- v ^ \v ^\ /v ^/), so that every out[] element sees
+// exactly the reference's sequence of fp32 additions (bit-exact for W >= H).  The
+// disparity vector of the previous pixel lives in registers spread over the lanes; L[d+-1]
+// come from two rotating shuffles per vector, min_k from one redux.sync on
+// order-preserving integer keys.  The next pixel's cost vector is prefetched while the
+// current one is being reduced.
+#include "lanevec.cuh"
+#include "sgm_paths.cuh"
+
+namespace stm {
+
+enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u };
+
+template <int NV, int VW>
+__global__ void __launch_bounds__(128)
+sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
+                float *__restrict__ out, int H, int W, int D, float p1, float p2, int dir,
+                int path_begin, int path_count, int min_limit, unsigned mode,
+                float *__restrict__ l_store, int l_store_path) {
+  const int lane = threadIdx.x & 31;
+  const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (w >= path_count) return;
+  const int path = path_begin + w;
+  const PathGeom g = sgm_path_geom(dir, path, H, W);
+  if (g.mult == 0) return;
+  const bool accumulate = mode & kSgmAccumulate;
+  const bool write_out = !(mode & kSgmNoOutput);
+  const bool store_l = (mode & kSgmStoreL) && path == l_store_path;
+  const int dpad = NV * 32 * VW;
+
+  int x = g.sx, y = g.sy;
+  size_t pix = (size_t)y * W + x;
+  LaneVec<NV, VW> L, c_next;
+  lv_load<NV, VW, true>(L, cost + pix * D, lane, D);
+  float prev_intensity = image[pix];
+
+  for (int i = 0; i < g.n; ++i) {
+    // prefetch the next pixel's cost vector and intensity
+    const bool has_next = i + 1 < g.n;
+    const int xn = x + g.dx, yn = y + g.dy;
+    const size_t pix_next = has_next ? (size_t)yn * W + xn : pix;
+    float intensity_next = 0.f;
+    if (has_next) {
+      lv_load<NV, VW, true>(c_next, cost + pix_next * D, lane, D);
+      intensity_next = image[pix_next];
+    }
+
+    // out[pix] (+)= L
+    if (write_out) {
+      LaneVec<NV, VW> o;
+      float *optr = out + pix * D;
+      if (accumulate) {
+        lv_load<NV, VW, true>(o, optr, lane, D);
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int j = 0; j < VW; ++j) o.v[k][j] += L.v[k][j];
+        lv_store<NV, VW, true>(o, optr, lane, D);
+      } else {
+        lv_store<NV, VW, true>(L, optr, lane, D);
+      }
+    }
+    if (store_l) lv_store<NV, VW, false>(L, l_store + (size_t)i * dpad, lane, dpad);
+
+    if (has_next) {
+      const float m = lv_min<NV, VW>(L, lane, min_limit);
+      LaneVec<NV, VW> lo, hi;
+      lv_neighbours<NV, VW>(L, lo, hi, lane);
+      const float q = p2 / fabsf(intensity_next - prev_intensity);
+      const float p2_adj = (p1 < q) ? q : p1;
+      const float far = m + p2_adj;
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int j = 0; j < VW; ++j) {
+          float best = L.v[k][j];
+          const float a = lo.v[k][j] + p1;
+          if (a < best) best = a;
+          const float b = hi.v[k][j] + p1;
+          if (b < best) best = b;
+          if (far < best) best = far;
+          L.v[k][j] = __fsub_rn(__fadd_rn(c_next.v[k][j], best), m);
+        }
+      prev_intensity = intensity_next;
+      x = xn;
+      y = yn;
+      pix = pix_next;
+    }
+  }
+}
+
+// Adds the stored path vector `times` more times, one fp32 addition at a time exactly as
+// the reference does when it re-runs the corner diagonal.
+__global__ void sgm_repeat_add_kernel(float *__restrict__ out, const float *__restrict__ l_store,
+                                      int W, int D, int dpad, int sx, int sy, int dx, int dy,
+                                      int n, int times) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * D) return;
+  const int i = t / D, d = t - i * D;
+  const size_t pix = (size_t)(sy + i * dy) * W + (sx + i * dx);
+  float s = out[pix * D + d];
+  const float l = l_store[(size_t)i * dpad + d];
+  for (int r = 0; r < times; ++r) s = __fadd_rn(s, l);
+  out[pix * D + d] = s;
+}
+
+template <int NV, int VW>
+static int run_direction(const float *cost, const float *image, float *out, int H, int W, int D,
+                         float p1, float p2, int dir, int path_begin, int path_count,
+                         int min_limit, unsigned mode, float *l_store, int l_store_path,
+                         cudaStream_t stream) {
+  const int warps = 4;
+  const int blocks = (path_count + warps - 1) / warps;
+  sgm_path_kernel<NV, VW><<<blocks, warps * 32, 0, stream>>>(
+      cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
+      l_store_path);
+  return check_launch("sgm_path_kernel");
+}
+
+static int repeat_add(float *out, float *l_store, int H, int W, int D, int dpad, int dir,
+                      int path, int times, cudaStream_t stream) {
+  const PathGeom g = sgm_path_geom(dir, path, H, W);
+  const int total = g.n * D;
+  sgm_repeat_add_kernel<<<(total + 255) / 256, 256, 0, stream>>>(out, l_store, W, D, dpad, g.sx,
+                                                                g.sy, g.dx, g.dy, g.n, times);
+  return check_launch("sgm_repeat_add_kernel");
+}
+
+template <int NV, int VW>
+static int sgm_by_direction(const float *cost, const float *image, float *out, int H, int W,
+                            int D, float p1, float p2, unsigned flags, float *ws,
+                            cudaStream_t stream) {
+  const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
+  const int dpad = NV * 32 * VW;
+  int rc;
+  for (int dir = 0; dir < 8; ++dir) {
+    const int np = sgm_num_paths(dir, H, W);
+    unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
+    const int multi = sgm_multi_path_index(dir, H, W);
+    if (multi < 0) {
+      rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, 0, np, min_limit, mode,
+                                 nullptr, -1, stream);
+      if (rc) return rc;
+      continue;
+    }
+    // landscape: the extra runs of the corner up-diagonal follow that diagonal's own
+    // forward+inverse pass in the reference's list order -> run the direction, then add
+    // the stored vector (mult-1) more times.
+    const int times = sgm_path_geom(dir, multi, H, W).mult - 1;
+    rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, 0, np, min_limit,
+                               mode | kSgmStoreL, ws, multi, stream);
+    if (rc) return rc;
+    if (times > 0) {
+      rc = repeat_add(out, ws, H, W, D, dpad, dir, multi, times, stream);
+      if (rc) return rc;
+    }
+  }
+  return STM_OK;
+}
+
+// Portrait images (H > W): the defective descriptors precede the corner diagonal's own
+// descriptor in the reference's list, so the extra (mult-1) additions of the dir-5 corner
+// path land BEFORE that diagonal's dir-4 and dir-5 contributions.  Same kernels, different
+// launch order: compute the corner path only (no output), add it mult-1 times, then run
+// dir 4 and dir 5 normally.
+template <int NV, int VW>
+static int sgm_by_direction_portrait(const float *cost, const float *image, float *out, int H,
+                                     int W, int D, float p1, float p2, unsigned flags, float *ws,
+                                     cudaStream_t stream) {
+  const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
+  const int dpad = NV * 32 * VW;
+  int rc;
+  for (int dir = 0; dir < 8; ++dir) {
+    const int np = sgm_num_paths(dir, H, W);
+    const unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
+    if (dir == 4) {
+      const int multi = sgm_multi_path_index(5, H, W);
+      const int times = sgm_path_geom(5, multi, H, W).mult - 1;
+      if (times > 0) {
+        rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 5, multi, 1, min_limit,
+                                   kSgmNoOutput | kSgmStoreL, ws, multi, stream);
+        if (rc) return rc;
+        rc = repeat_add(out, ws, H, W, D, dpad, 5, multi, times, stream);
+        if (rc) return rc;
+      }
+    }
+    rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, 0, np, min_limit, mode,
+                               nullptr, -1, stream);
+    if (rc) return rc;
+  }
+  return STM_OK;
+}
+
+size_t sgm_workspace_bytes(int H, int W, int D) {
+  const LaneMap m = pick_lane_map(D);
+  const size_t dpad = (size_t)m.NV * 32 * m.VW;
+  return (size_t)(H < W ? H : W) * dpad * sizeof(float);
+}
+
+int launch_sgm(const float *cost, const float *image, float *out, int H, int W, int D, float p1,
+               float p2, unsigned flags, void *workspace, size_t workspace_bytes,
+               cudaStream_t stream) {
+  if (D < 2) return fail(STM_EINVAL, "sgm: D must be >= 2");
+  if (H > 32767 || W > 32767)  // the reference stores coordinates as int16 (semiglobal.hpp:34-36)
+    return fail(STM_EINVAL, "sgm: H and W must be <= 32767");
+  if (workspace_bytes < sgm_workspace_bytes(H, W, D) || (workspace == nullptr && H != W))
+    return fail(STM_EINVAL, "sgm: workspace too small (%zu < %zu)", workspace_bytes,
+                sgm_workspace_bytes(H, W, D));
+  const LaneMap m = pick_lane_map(D);
+  float *ws = static_cast<float *>(workspace);
+#define STM_SGM_CASE(NV_, VW_)                                                            \
+  if (m.NV == NV_ && m.VW == VW_)                                                         \
+    return H > W ? sgm_by_direction_portrait<NV_, VW_>(cost, image, out, H, W, D, p1, p2,  \
+                                                       flags, ws, stream)                 \
+                 : sgm_by_direction<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags,    \
+                                              ws, stream);
+  STM_SGM_CASE(1, 4) STM_SGM_CASE(2, 4) STM_SGM_CASE(3, 4) STM_SGM_CASE(4, 4)
+  STM_SGM_CASE(1, 2) STM_SGM_CASE(3, 2) STM_SGM_CASE(5, 2) STM_SGM_CASE(7, 2)
+  STM_SGM_CASE(1, 1) STM_SGM_CASE(2, 1) STM_SGM_CASE(3, 1) STM_SGM_CASE(4, 1)
+  STM_SGM_CASE(5, 1) STM_SGM_CASE(6, 1) STM_SGM_CASE(7, 1) STM_SGM_CASE(8, 1)
+#undef STM_SGM_CASE
+  return fail(STM_EUNSUPPORTED, "sgm: D=%d not supported (D <= 512 if D %% 128 == 0, <= 448 if "
+              "D %% 64 == 0, else <= 256)", D);
+}
+
+}  // namespace stm

@@ -1,0 +1,38 @@
+"""Cost-volume aggregation (API of reference stereomatch/aggregation.py)."""
+from typing import Optional
+
+import torch
+
+from ._common import empty_tensor
+from ._cstereomatch import STM_SGM_MIN_ALL_D, STM_SGM_OVERWRITE
+from ._cstereomatch import AggregationOps as _AggregationOps
+
+
+class Semiglobal:
+    """Semiglobal matching aggregation over the reference's path set: 8 directions with
+    the adaptive second penalty max(P1, P2/|dI|) (reference stereomatch/aggregation.py:13-57,
+    src/semiglobal.cpp:116-159).
+
+    penalty1 / penalty2 are public and mutable as in the reference.  Keyword-only extra:
+    min_over_all_d=False keeps the compiled CPU reference's min over d in [0, D-2]
+    (SURVEY F6); True takes the min over all D like the reference CUDA kernel.
+    Unlike the reference's CUDA branch, D does not have to be a power of two.
+    """
+
+    def __init__(self, penalty1: float = 0.1, penalty2: float = 0.2, *,
+                 min_over_all_d: bool = False):
+        self.penalty1 = penalty1
+        self.penalty2 = penalty2
+        self.min_over_all_d = min_over_all_d
+
+    def __call__(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
+                 sga_volume: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """[H,W,D] cost volume + [H,W] left image -> [H,W,D] aggregated volume.  The result
+        equals the reference's zero-fill followed by accumulation; the zero fill itself
+        is skipped (the first direction overwrites)."""
+        sga_volume = empty_tensor(*cost_volume.size(), dtype=cost_volume.dtype,
+                                  device=cost_volume.device, reuse_tensor=sga_volume)
+        flags = STM_SGM_OVERWRITE | (STM_SGM_MIN_ALL_D if self.min_over_all_d else 0)
+        _AggregationOps.run_semiglobal(cost_volume, left_image, self.penalty1, self.penalty2,
+                                       sga_volume, flags)
+        return sga_volume

@@ -1,0 +1,52 @@
+"""Matching-cost volumes (API of reference stereomatch/cost.py)."""
+from typing import Optional
+
+import torch
+
+from ._common import empty_tensor
+from ._cstereomatch import CostOps as _CostOps
+
+
+class SSD:
+    """Windowed sum of squared differences (reference stereomatch/cost.py:13-48).
+
+    Attributes (public and mutable, as in the reference): max_disparity, kernel_size
+    (half-width of the half-open 2k x 2k window, reference src/ssd.cu:36-42),
+    cost_volume_dtype (float32 is the only dtype the reference's dispatch accepts).
+    """
+
+    def __init__(self, max_disparity: int, kernel_size: int = 7,
+                 cost_volume_dtype: torch.dtype = torch.float):
+        self.max_disparity = max_disparity
+        self.kernel_size = kernel_size
+        self.cost_volume_dtype = cost_volume_dtype
+
+    def __call__(self, left_image: torch.Tensor, right_image: torch.Tensor,
+                 cost_volume: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """[H,W] x [H,W] float32 CUDA images -> [H,W,max_disparity] cost volume
+        (+inf where d > x)."""
+        cost_volume = empty_tensor(left_image.size(0), left_image.size(1), self.max_disparity,
+                                   dtype=self.cost_volume_dtype, device=left_image.device,
+                                   reuse_tensor=cost_volume)
+        _CostOps.compute_ssd(left_image, right_image, cost_volume, self.kernel_size)
+        return cost_volume
+
+
+class Birchfield:
+    """Birchfield-Tomasi sampling-insensitive cost, 1-D window of 8 taps
+    (reference stereomatch/cost.py:80-101; the reference ignores kernel_size and always
+    uses 4, reference src/birchfield_cost.cu:159).  Entries d > x, which the reference
+    leaves unwritten, are +inf."""
+
+    def __init__(self, max_disparity: int, kernel_size: int = 7):
+        self.max_disparity = max_disparity
+        self.kernel_size = kernel_size
+        self.kerne_size = kernel_size  # the reference's (misspelt) attribute, cost.py:90
+
+    def __call__(self, left_image: torch.Tensor, right_image: torch.Tensor,
+                 cost_volume: Optional[torch.Tensor] = None) -> torch.Tensor:
+        cost_volume = empty_tensor(left_image.size(0), left_image.size(1), self.max_disparity,
+                                   dtype=torch.float32, device=left_image.device,
+                                   reuse_tensor=cost_volume)
+        _CostOps.compute_birchfield(left_image.float(), right_image.float(), cost_volume, 4)
+        return cost_volume

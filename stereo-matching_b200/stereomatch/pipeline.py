@@ -1,0 +1,37 @@
+"""cost -> (aggregation) -> disparity reduce (API of reference stereomatch/pipeline.py:36-94)."""
+from typing import Callable, Optional
+
+import torch
+
+CostFunction = Callable[[torch.Tensor, torch.Tensor, torch.Tensor], torch.Tensor]
+AggregationFunction = Callable[[torch.Tensor, torch.Tensor, torch.Tensor], torch.Tensor]
+DisparityReduceFunction = Callable[[torch.Tensor, torch.Tensor], torch.Tensor]
+
+
+class Pipeline:
+    """Composes the three stages and keeps their output buffers between frames, so a
+    steady-state video loop allocates nothing (reference pipeline.py:65-67, 80-92)."""
+
+    def __init__(self, cost: CostFunction, disparity_reduce: DisparityReduceFunction,
+                 aggregation: Optional[AggregationFunction] = None):
+        self.cost = cost
+        self.disparity_reduce = disparity_reduce
+        self.aggregation = aggregation
+        self._cost_volume = None
+        self._aggregation_volume = None
+        self._disparity_image = None
+
+    def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor) -> torch.Tensor:
+        """[H,W] left/right images (CUDA float32) -> int32 [H,W] disparity map."""
+        self._cost_volume = self.cost(left_image, right_image, cost_volume=self._cost_volume)
+        if self.aggregation is not None:
+            own = self._aggregation_volume
+            if own is self._cost_volume:  # left over from a run without aggregation
+                own = None
+            self._aggregation_volume = self.aggregation(
+                self._cost_volume, left_image.to(self._cost_volume.device), own)
+        else:
+            self._aggregation_volume = self._cost_volume
+        self._disparity_image = self.disparity_reduce(self._aggregation_volume,
+                                                      self._disparity_image)
+        return self._disparity_image

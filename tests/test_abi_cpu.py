@@ -1,0 +1,105 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/stm_abi.h
+declares, the Python API mirrors the reference's, and nothing computes without a GPU."""
+import ctypes
+import re
+from pathlib import Path
+
+import pytest
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+HEADER = ROOT / "include" / "stm_abi.h"
+LIB = ROOT / "stereo-matching_b200" / "stereomatch" / "libstm_b200.so"
+
+
+def declared_symbols():
+    text = re.sub(r"/\*.*?\*/", "", HEADER.read_text(), flags=re.S)
+    return sorted(set(re.findall(r"\b(stm_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    assert LIB.exists(), "run python stereo-matching_b200/build.py"
+    lib = ctypes.CDLL(str(LIB))
+    names = declared_symbols()
+    assert len(names) >= 10
+    for n in names:
+        assert hasattr(lib, n), n
+
+
+def test_version_and_error_strings():
+    lib = ctypes.CDLL(str(LIB))
+    lib.stm_version.restype = ctypes.c_char_p
+    lib.stm_last_error.restype = ctypes.c_char_p
+    assert b"sm_100a" in lib.stm_version()
+    # bad shape is rejected before any CUDA call
+    rc = lib.stm_wta_f32(None, None, 0, 4, 4, None)
+    assert rc == -1 and b"invalid shape" in lib.stm_last_error()
+
+
+def test_workspace_query_is_pure():
+    lib = ctypes.CDLL(str(LIB))
+    lib.stm_sgm_workspace_bytes.restype = ctypes.c_size_t
+    assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == 1080 * 128 * 4
+    assert lib.stm_sgm_workspace_bytes(30, 18, 16) == 18 * 32 * 4
+    assert lib.stm_sgm_workspace_bytes(0, 0, 0) == 0
+
+
+def test_python_api_surface_matches_reference():
+    import stereomatch
+    from stereomatch import aggregation, cost, disparity_reduce, pipeline
+    ssd = cost.SSD(64)
+    assert (ssd.max_disparity, ssd.kernel_size, ssd.cost_volume_dtype) == (64, 7, torch.float32)
+    ssd.max_disparity = 32  # attributes stay mutable (reference workflow.py:34)
+    bt = cost.Birchfield(32)
+    assert bt.max_disparity == 32 and bt.kerne_size == 7
+    sgm = aggregation.Semiglobal()
+    assert (sgm.penalty1, sgm.penalty2) == (0.1, 0.2)
+    p = pipeline.Pipeline(ssd, disparity_reduce.WinnerTakesAll(), sgm)
+    assert p.cost is ssd and p.aggregation is sgm
+    assert hasattr(disparity_reduce.DynamicProgramming(), "__call__")
+    assert stereomatch.Pipeline is pipeline.Pipeline
+
+
+def test_no_cpu_fallback():
+    from stereomatch import aggregation, cost, disparity_reduce
+    img = torch.zeros(8, 8)
+    vol = torch.zeros(8, 8, 4)
+    with pytest.raises(RuntimeError, match="gpu tensor"):
+        cost.SSD(4)(img, img)
+    with pytest.raises(RuntimeError, match="gpu tensor"):
+        cost.Birchfield(4)(img, img)
+    with pytest.raises(RuntimeError, match="gpu tensor"):
+        aggregation.Semiglobal()(vol, img)
+    with pytest.raises(RuntimeError, match="gpu tensor"):
+        disparity_reduce.WinnerTakesAll()(vol)
+    with pytest.raises(RuntimeError, match="gpu tensor"):
+        disparity_reduce.DynamicProgramming()(vol)
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="only meaningful without a GPU")
+def test_compute_call_fails_loudly_without_gpu():
+    lib = ctypes.CDLL(str(LIB))
+    lib.stm_last_error.restype = ctypes.c_char_p
+    buf = (ctypes.c_float * 64)()
+    out = (ctypes.c_int32 * 16)()
+    rc = lib.stm_wta_f32(buf, out, 4, 4, 4, None)
+    assert rc == -2 and b"no CPU fallback" in lib.stm_last_error()
+
+
+def test_numeric_known_answers():
+    from stereomatch.numeric import is_power_of_two, next_power_of_2
+    # reference tests/test_numeric.py:11-17
+    for n, e in [(0, 1), (1, 1), (2, 2), (3, 4), (4, 4), (50, 64), (127, 128)]:
+        assert next_power_of_2(n) == e
+    assert is_power_of_two(64) and not is_power_of_two(0) and not is_power_of_two(192)
+
+
+def test_buffer_reuse_rules():
+    from stereomatch._common import empty_tensor, zeros_tensor_like
+    a = torch.ones(3, 4)
+    assert empty_tensor(3, 4, reuse_tensor=a) is a
+    assert empty_tensor(3, 5, reuse_tensor=a) is not a
+    assert empty_tensor(3, 4, dtype=torch.int32, reuse_tensor=a).dtype == torch.int32
+    z = zeros_tensor_like(a, reuse_tensor=a)
+    assert z is a and float(a.sum()) == 0.0
+    assert zeros_tensor_like(a, reuse_tensor=torch.ones(2, 2)).shape == (3, 4)

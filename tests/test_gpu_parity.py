@@ -1,0 +1,300 @@
+"""Parity of the CUDA path (through the C ABI / the reference-shaped Python API) against
+the oracle and the committed golden vectors.  Run on the B200 box: pytest -m gpu.
+
+Bars (BASELINE.json): WTA / DP maps bit-exact given identical volumes; cost volumes and
+SGM sums within 1e-4 relative on finite entries with an identical inf pattern
+(RTOL below); end-to-end maps differ at <= 0.1 % of pixels.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O, synth
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4  # north_star: "float cost volumes and SGM aggregated costs within 1e-4 relative"
+
+
+@pytest.fixture(scope="module")
+def sm():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import stereomatch
+    return stereomatch
+
+
+def cuda(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def assert_volume_close(got, want, exact=False):
+    got = got.cpu().numpy() if isinstance(got, torch.Tensor) else got
+    assert got.shape == want.shape
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin), "inf pattern differs"
+    assert np.array_equal(got[~fin], want[~fin]) or np.array_equal(
+        np.isposinf(got[~fin]), np.isposinf(want[~fin]))
+    if exact:
+        assert np.array_equal(got[fin], want[fin])
+        return 0.0
+    denom = np.maximum(np.abs(want[fin]), np.abs(got[fin]))
+    err = np.abs(got[fin] - want[fin])
+    rel = np.where(denom > 0, err / np.where(denom > 0, denom, 1), 0.0)
+    assert rel.max(initial=0.0) <= RTOL, f"max rel err {rel.max()}"
+    return float(rel.max(initial=0.0))
+
+
+# ------------------------------------------------------------------------------ costs
+COST_CASES = ["cost_raw_24x40x16", "cost_unit_40x24x16", "cost_unit_20x72x32"]
+
+
+@pytest.mark.parametrize("case", COST_CASES)
+def test_ssd_golden(sm, golden, case):
+    g = golden(case)
+    D = g["ssd7"].shape[2]
+    l, r = cuda(g["left"]), cuda(g["right"])
+    assert_volume_close(sm.cost.SSD(D, 7)(l, r), g["ssd7"], exact="raw" in case)
+    assert_volume_close(sm.cost.SSD(D, 3)(l, r), g["ssd3"], exact="raw" in case)
+
+
+@pytest.mark.parametrize("H,W,D,k,scale", [
+    (37, 53, 32, 7, "raw"), (37, 53, 32, 7, "unit"), (19, 140, 64, 7, "unit"),
+    (50, 31, 128, 7, "raw"), (23, 70, 192, 7, "unit"), (9, 11, 5, 2, "unit"),
+    (16, 33, 32, 0, "raw"), (40, 200, 128, 7, "unit"),
+])
+def test_ssd_vs_oracle(sm, H, W, D, k, scale):
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=H + W, scale=scale)
+    got = sm.cost.SSD(D, k)(cuda(left), cuda(right))
+    assert_volume_close(got, O.ssd(left, right, D, k), exact=(scale == "raw"))
+
+
+@pytest.mark.parametrize("case", COST_CASES)
+def test_birchfield_golden_shift_relation(sm, golden, case):
+    """Against the compiled reference CPU op under the one-pixel shift relation."""
+    g = golden(case)
+    ref = g["bt_cpu"]
+    H, W, D = ref.shape
+    got = sm.cost.Birchfield(D)(cuda(g["left"]), cuda(g["right"])).cpu().numpy()
+    for x in range(4, W - 6):
+        dm = min(D, x - 3)
+        a, b = got[:-1, x + 1, :dm], ref[:-1, x, :dm]
+        assert np.allclose(a, b, rtol=RTOL, atol=0)
+
+
+@pytest.mark.parametrize("H,W,D,scale", [(21, 45, 16, "raw"), (21, 45, 32, "unit"),
+                                           (12, 150, 128, "unit"), (30, 9, 64, "raw"),
+                                           (8, 70, 192, "unit")])
+def test_birchfield_vs_oracle(sm, H, W, D, scale):
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=3 * H + W, scale=scale)
+    got = sm.cost.Birchfield(D)(cuda(left), cuda(right))
+    assert_volume_close(got, O.birchfield(left, right, D), exact=(scale == "raw"))
+
+
+# -------------------------------------------------------------------------------- SGM
+SGM_CASES = ["sgm_unit_18x30x16", "sgm_unit_30x18x16", "sgm_raw_16x16x32",
+             "sgm_raw_12x40x64", "sgm_minlast_14x22x8"]
+
+
+@pytest.mark.parametrize("case", SGM_CASES)
+def test_sgm_golden(sm, golden, case):
+    g = golden(case)
+    agg = sm.aggregation.Semiglobal(float(g["p"][0]), float(g["p"][1]))(cuda(g["cost"]),
+                                                                       cuda(g["left"]))
+    assert_volume_close(agg, g["agg"])
+    # given the reference's aggregated volume, WTA is bit-exact
+    assert np.array_equal(sm.disparity_reduce.WinnerTakesAll()(cuda(g["agg"])).cpu().numpy(),
+                          g["wta"])
+
+
+@pytest.mark.parametrize("H,W,D,scale,p1,p2,all_d", [
+    (26, 41, 32, "unit", 0.1, 0.2, False), (41, 26, 32, "unit", 0.1, 0.2, False),
+    (20, 20, 64, "raw", 20.0, 90.0, False), (17, 60, 128, "unit", 0.1, 0.2, False),
+    (17, 60, 128, "raw", 50.0, 200.0, True), (13, 35, 192, "unit", 0.1, 0.2, False),
+    (35, 13, 96, "unit", 0.3, 1.0, True), (11, 29, 20, "raw", 5.0, 9.0, False),
+    (1, 9, 32, "unit", 0.1, 0.2, False), (9, 1, 32, "unit", 0.1, 0.2, False),
+])
+def test_sgm_vs_oracle(sm, H, W, D, scale, p1, p2, all_d):
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 7 + W, scale=scale)
+    cost = O.ssd(left, right, D, 3)
+    want = O.sgm(cost, left, p1, p2, min_over_all_d=all_d)
+    got = sm.aggregation.Semiglobal(p1, p2, min_over_all_d=all_d)(cuda(cost), cuda(left))
+    assert_volume_close(got, want)
+
+
+def test_sgm_accumulates_like_the_reference(sm):
+    """The raw op ACCUMULATES into the caller's volume (reference aggregation.py:51)."""
+    from stereomatch._cstereomatch import AggregationOps
+    H, W, D = 12, 20, 32
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=5, scale="unit")
+    cost = O.ssd(left, right, D, 3)
+    base = synth.random_volume(H, W, D, seed=6, hi=3.0)
+    out = cuda(base.copy())
+    AggregationOps.run_semiglobal(cuda(cost), cuda(left), 0.1, 0.2, out)
+    want = O.sgm(cost, left, 0.1, 0.2, out=base.copy())
+    assert_volume_close(out, want)
+
+
+def test_sgm_reference_arange_recipe(sm):
+    """The reference's own equality-test input (tests/test_semiglobalmatch.py:46-47), smaller."""
+    H = W = 40
+    D = 128
+    vol = np.arange(H * W * D, dtype=np.float32).reshape(H, W, D)
+    img = np.ones((H, W), np.float32)
+    got = sm.aggregation.Semiglobal()(cuda(vol), cuda(img))
+    assert_volume_close(got, O.sgm(vol, img, 0.1, 0.2))
+
+
+# -------------------------------------------------------------------------------- WTA
+@pytest.mark.parametrize("case", ["wta_ties_16x24x32", "wta_rand_9x13x192"])
+def test_wta_golden(sm, golden, case):
+    g = golden(case)
+    got = sm.disparity_reduce.WinnerTakesAll()(cuda(g["cost"])).cpu().numpy()
+    assert np.array_equal(got, g["wta"])
+
+
+@pytest.mark.parametrize("H,W,D", [(7, 9, 1), (7, 9, 3), (5, 11, 4), (13, 17, 30), (33, 31, 64),
+                                     (10, 23, 128), (6, 7, 192), (3, 5, 1000)])
+def test_wta_vs_oracle_adversarial(sm, H, W, D):
+    vol = synth.tie_heavy_volume(H, W, D, seed=D)
+    vol[0, 0, :] = np.inf
+    vol[0, 1, 0] = np.nan
+    vol[0, 2, D // 2] = np.nan
+    vol[0, 3, :] = np.nan
+    vol[1, :, : D // 2] = np.inf
+    vol[2, :, :] = -vol[2, :, :]
+    got = sm.disparity_reduce.WinnerTakesAll()(cuda(vol)).cpu().numpy()
+    assert np.array_equal(got, O.wta(vol))
+
+
+# --------------------------------------------------------------------------------- DP
+@pytest.mark.parametrize("case", ["dp_raw_32x48x16", "dp_raw_32x32x32", "dp_ties_16x20x8"])
+def test_dp_cpu_exact_golden(sm, golden, case):
+    g = golden(case)
+    dp = sm.disparity_reduce.DynamicProgramming(mode="cpu_exact")
+    got = dp(cuda(g["cost"])).cpu().numpy()
+    assert np.array_equal(got, g["disp"])
+    assert np.array_equal(dp._row_final_costs.cpu().numpy(), g["row_final"])
+    assert np.array_equal(dp._path_volume.cpu().numpy(), g["path"])
+
+
+@pytest.mark.parametrize("H,W,D,kind", [(20, 50, 32, "ssd"), (9, 33, 64, "ssd"), (12, 40, 128, "ssd"),
+                                          (7, 30, 192, "ssd"), (15, 21, 12, "ties"), (6, 1, 32, "ties"),
+                                          (5, 64, 96, "rand")])
+def test_dp_cuda_mode_vs_oracle(sm, H, W, D, kind):
+    if kind == "ssd":
+        left, right, _ = synth.random_dot_pair(H, W, D, seed=H + D, scale="raw")
+        vol = O.ssd(left, right, D, 3)
+    elif kind == "ties":
+        vol = synth.tie_heavy_volume(H, W, D, seed=D)
+    else:
+        vol = synth.random_volume(H, W, D, seed=D)
+    dp = sm.disparity_reduce.DynamicProgramming()
+    got = dp(cuda(vol)).cpu().numpy()
+    want, wpath, wfinal = O.dp(vol, "cuda", return_aux=True)
+    assert np.array_equal(got, want)
+    assert np.array_equal(dp._row_final_costs.cpu().numpy(), wfinal)
+    assert np.array_equal(dp._path_volume.cpu().numpy()[:, 1:], wpath[:, 1:])
+
+
+# --------------------------------------------------------------------------- pipeline
+@pytest.mark.parametrize("cost_name,agg,red", [("SSD", True, "wta"), ("SSD", False, "wta"),
+                                               ("Birchfield", True, "wta"), ("SSD", False, "dp"),
+                                               ("Birchfield", False, "dp")])
+def test_pipeline_end_to_end(sm, cost_name, agg, red):
+    H, W, D = 48, 96, 32
+    left, right, gt = synth.random_dot_pair(H, W, D, seed=99, scale="unit")
+    cost_fn = sm.cost.SSD(D) if cost_name == "SSD" else sm.cost.Birchfield(D)
+    reducer = sm.disparity_reduce.WinnerTakesAll() if red == "wta" else \
+        sm.disparity_reduce.DynamicProgramming()
+    pipe = sm.Pipeline(cost_fn, reducer, sm.aggregation.Semiglobal() if agg else None)
+    got = pipe.estimate(cuda(left), cuda(right))
+    first_ptr = got.data_ptr()
+    got = pipe.estimate(cuda(left), cuda(right))  # second frame reuses every buffer
+    assert got.data_ptr() == first_ptr and got.dtype == torch.int32
+    vol = O.ssd(left, right, D, 7) if cost_name == "SSD" else O.birchfield(left, right, D)
+    if agg:
+        vol = O.sgm(vol, left, 0.1, 0.2)
+    want = O.wta(vol) if red == "wta" else O.dp(vol, "cuda")
+    mismatch = float((got.cpu().numpy() != want).mean())
+    assert mismatch <= 1e-3, mismatch  # north_star: <= 0.1 % of pixels
+
+
+def test_pipeline_host_entry_point(sm):
+    """stm_pipeline_host_f32: host buffers in, host map out, copies inside the call."""
+    from stereomatch import _cstereomatch as C
+    H, W, D = 40, 72, 64
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=123, scale="unit")
+    got = C.pipeline_host(torch.from_numpy(left), torch.from_numpy(right), D).numpy()
+    want = O.wta(O.sgm(O.ssd(left, right, D, 7), left, 0.1, 0.2))
+    assert float((got != want).mean()) <= 1e-3
+    got = C.pipeline_host(torch.from_numpy(left), torch.from_numpy(right), D, use_sgm=False,
+                          reducer=1).numpy()
+    assert np.array_equal(got, O.dp(O.ssd(left, right, D, 7), "cuda"))
+
+
+def test_errors_mirror_the_reference(sm):
+    img = torch.zeros(8, 8, device="cuda")
+    with pytest.raises(RuntimeError, match="type not supported"):
+        sm.cost.SSD(4)(img.to(torch.uint8), img.to(torch.uint8))
+    with pytest.raises(RuntimeError, match="gpu tensor"):
+        sm.cost.SSD(4)(img, img.cpu())
+    with pytest.raises(RuntimeError, match="D <= H <= W"):
+        sm.disparity_reduce.DynamicProgramming(mode="cpu_exact")(torch.zeros(4, 8, 16, device="cuda"))
+
+
+# ------------------------------------------------- full-size, size-independent properties
+def test_full_size_1080p_properties(sm):
+    """1920x1080 D=128: properties that need no CPU oracle run."""
+    H, W, D = 1080, 1920, 128
+    left, right, gt = synth.random_dot_pair(H, W, D, seed=1000, scale="raw")
+    l, r = cuda(left), cuda(right)
+    cost = sm.cost.SSD(D)(l, r)
+    # (1) d > x is +inf, everything else finite and >= 0
+    dd = torch.arange(D, device="cuda")[None, :]
+    xx = torch.arange(W, device="cuda")[:, None]
+    assert bool(torch.isinf(cost[:, dd.expand(W, D) > xx]).all())
+    assert bool((cost[:, dd.expand(W, D) <= xx] >= 0).all())
+    # (2) a band of rows against the oracle (bit-exact on integer-valued images)
+    band = slice(533, 547)
+    want = O.ssd(left[band.start - 7:band.stop + 7], right[band.start - 7:band.stop + 7], D, 7)[7:-7]
+    assert np.array_equal(cost[band].cpu().numpy(), want)
+    # (3) WTA == torch.argmin on NaN-free volumes, and recovers the ground truth
+    wta = sm.disparity_reduce.WinnerTakesAll()(cost)
+    assert bool((wta.long() == torch.argmin(cost, dim=2)).all())
+    valid = torch.from_numpy(np.arange(W)[None, :] >= gt + 7).cuda()
+    acc = float((wta[valid] == cuda(gt)[valid]).float().mean())
+    assert acc > 0.99, acc
+    # (4) SGM: linear in the cost volume's positive scale when penalties scale too
+    sgm = sm.aggregation.Semiglobal(30.0, 120.0)
+    agg = sgm(cost, l)
+    agg2 = sm.aggregation.Semiglobal(60.0, 240.0)(cost * 2, l)
+    fin = torch.isfinite(agg)
+    assert bool((torch.isfinite(agg2) == fin).all())
+    assert bool(torch.equal(agg2[fin], agg[fin] * 2))  # power-of-two scaling is exact in fp32
+    # (5) a path-local check: the first row only sees -> <- and the starts of v \v /v
+    #     so a 3-row crop reproduces row 0 of `->`+`<-` ... use the oracle on a narrow crop
+    #     of full width is too slow; instead check SGM+WTA recovers the ground truth.
+    wta2 = sm.disparity_reduce.WinnerTakesAll()(agg)
+    acc2 = float((wta2[valid] == cuda(gt)[valid]).float().mean())
+    assert acc2 > 0.99, acc2
+    # (6) DP runs at full size and returns in-range disparities; its forward costs are
+    #     reproducible (same input -> identical output)
+    dp = sm.disparity_reduce.DynamicProgramming()
+    d1 = dp(cost).clone()
+    d2 = dp(cost)
+    assert bool(torch.equal(d1, d2)) and int(d1.min()) >= 0 and int(d1.max()) < D
+
+
+def test_full_height_sgm_column_strip_vs_oracle(sm):
+    """Full-height (1080 rows), narrow strip: exercises long paths and the 1080-fold
+    corner-diagonal multiplicity against the oracle."""
+    H, W, D = 1080, 24, 32
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=77, scale="unit")
+    cost = O.ssd(left, right, D, 3)
+    got = sm.aggregation.Semiglobal()(cuda(cost), cuda(left))
+    assert_volume_close(got, O.sgm(cost, left, 0.1, 0.2))
+    H, W = 24, 1100
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=78, scale="unit")
+    cost = O.ssd(left, right, D, 3)
+    got = sm.aggregation.Semiglobal()(cuda(cost), cuda(left))
+    assert_volume_close(got, O.sgm(cost, left, 0.1, 0.2))
