@@ -28,6 +28,7 @@ dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= H) return;
   const size_t row_off = (size_t)row * W;
+  const LaneCtx cx = lv_ctx<NV, VW>(lane, D);
 
   LaneVec<NV, VW> acc, c_next;
   lv_load<NV, VW, true>(acc, cost + row_off * D, lane, D);
@@ -48,7 +49,7 @@ dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
     LaneVec<NV, VW> cur = c_next;
     if (col + 1 < W) lv_load<NV, VW, true>(c_next, cost + (row_off + col + 1) * D, lane, D);
     LaneVec<NV, VW> lo, hi;
-    lv_neighbours<NV, VW>(acc, lo, hi, lane);
+    lv_neighbours<NV, VW>(acc, lo, hi, cx);
     int8_t *pp = path + (row_off + col) * D;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {

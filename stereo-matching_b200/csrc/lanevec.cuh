@@ -54,41 +54,92 @@ __device__ __forceinline__ void lv_store(const LaneVec<NV, VW> &r, float *__rest
   }
 }
 
+// Per-lane constants of the lane<->disparity map, computed once per kernel.
+struct LaneCtx {
+  int src_lo, src_hi;  // rotating shuffle sources: lane-1, lane+1
+  bool first, last;    // lane 0 / lane 31
+  bool excl_last;      // this lane's last slot [NV-1][VW-1] holds a disparity >= min limit
+};
+
+template <int NV, int VW>
+__device__ __forceinline__ LaneCtx lv_ctx(int lane, int min_limit) {
+  LaneCtx c;
+  c.src_lo = (lane + 31) & 31;
+  c.src_hi = (lane + 1) & 31;
+  c.first = lane == 0;
+  c.last = lane == 31;
+  // The only disparity ever excluded from the minimum is D-1 (and the +inf padding above
+  // it), and it always sits in the last slot of its lane (see sgm_paths.cuh).
+  c.excl_last = lv_d<NV, VW>(lane, NV - 1, VW - 1) >= min_limit;
+  return c;
+}
+
+// Warp-wide float minimum: one redux.sync.min.f32 (CREDUX.MIN.F32 on sm_100a).
+__device__ __forceinline__ float warp_min_f32(float v) {
+  float r;
+  asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+
 // lo[k][j] = value at d-1, hi[k][j] = value at d+1 (+inf outside [0, Dpad)).
 template <int NV, int VW>
 __device__ __forceinline__ void lv_neighbours(const LaneVec<NV, VW> &a, LaneVec<NV, VW> &lo,
-                                              LaneVec<NV, VW> &hi, int lane) {
+                                              LaneVec<NV, VW> &hi, const LaneCtx &cx) {
   float from_left[NV], from_right[NV];
 #pragma unroll
   for (int k = 0; k < NV; ++k) {
-    from_left[k] = __shfl_sync(FULL, a.v[k][VW - 1], (lane + 31) & 31);  // lane-1 (rotating)
-    from_right[k] = __shfl_sync(FULL, a.v[k][0], (lane + 1) & 31);       // lane+1 (rotating)
+    from_left[k] = __shfl_sync(FULL, a.v[k][VW - 1], cx.src_lo);
+    from_right[k] = __shfl_sync(FULL, a.v[k][0], cx.src_hi);
   }
 #pragma unroll
   for (int k = 0; k < NV; ++k) {
 #pragma unroll
     for (int j = 0; j < VW; ++j) {
       if (j > 0) lo.v[k][j] = a.v[k][j - 1];
-      else lo.v[k][j] = lane > 0 ? from_left[k] : (k > 0 ? from_left[k > 0 ? k - 1 : 0] : CUDART_INF_F);
+      else lo.v[k][j] = cx.first ? (k > 0 ? from_left[k > 0 ? k - 1 : 0] : CUDART_INF_F) : from_left[k];
       if (j < VW - 1) hi.v[k][j] = a.v[k][j + 1];
-      else hi.v[k][j] = lane < 31 ? from_right[k]
-                                  : (k < NV - 1 ? from_right[k < NV - 1 ? k + 1 : k] : CUDART_INF_F);
+      else hi.v[k][j] = cx.last ? (k < NV - 1 ? from_right[k < NV - 1 ? k + 1 : k] : CUDART_INF_F)
+                                : from_right[k];
     }
   }
 }
 
-// Minimum over d in [0, limit) of the vector (limit = D or D-1).
+// Minimum over the disparities below the limit the context was built with.
 template <int NV, int VW>
-__device__ __forceinline__ float lv_min(const LaneVec<NV, VW> &a, int lane, int limit) {
-  float m = CUDART_INF_F;
+__device__ __forceinline__ float lv_min(const LaneVec<NV, VW> &a, const LaneCtx &cx) {
+  float m = cx.excl_last ? CUDART_INF_F : a.v[NV - 1][VW - 1];
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int j = 0; j < VW; ++j)
+      if (!(k == NV - 1 && j == VW - 1)) m = fminf(m, a.v[k][j]);
+  return warp_min_f32(m);
+}
+
+// One step of the SGM recurrence (reference src/semiglobal.cpp:145-156):
+//   L[d] = (c[d] + min(L[d], L[d-1]+P1, L[d+1]+P1, m+P2')) - m
+template <int NV, int VW>
+__device__ __forceinline__ void lv_sgm_step(LaneVec<NV, VW> &L, const LaneVec<NV, VW> &c, float p1,
+                                            float p2_adj, const LaneCtx &cx) {
+  const float m = lv_min<NV, VW>(L, cx);
+  LaneVec<NV, VW> lo, hi;
+  lv_neighbours<NV, VW>(L, lo, hi, cx);
+  const float far = __fadd_rn(m, p2_adj);
 #pragma unroll
   for (int k = 0; k < NV; ++k)
 #pragma unroll
     for (int j = 0; j < VW; ++j) {
-      const float x = a.v[k][j];
-      if (lv_d<NV, VW>(lane, k, j) < limit) m = fminf(m, x);
+      const float a = __fadd_rn(lo.v[k][j], p1);
+      const float b = __fadd_rn(hi.v[k][j], p1);
+      const float best = fminf(fminf(L.v[k][j], a), fminf(b, far));
+      L.v[k][j] = __fsub_rn(__fadd_rn(c.v[k][j], best), m);
     }
-  return warp_min(m);
+}
+
+// max(P1, P2/|dI|) with std::max semantics (x/0 = inf, 0/0 = NaN -> P1), IEEE division.
+__device__ __forceinline__ float sgm_p2_adjusted(float p1, float p2, float intensity, float prev) {
+  const float q = __fdiv_rn(p2, fabsf(__fsub_rn(intensity, prev)));
+  return (p1 < q) ? q : p1;
 }
 
 }  // namespace stm

@@ -23,7 +23,7 @@ namespace stm {
 
 enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u };
 
-template <int NV, int VW>
+template <int NV, int VW, bool ACC>
 __global__ void __launch_bounds__(128)
 sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
                 float *__restrict__ out, int H, int W, int D, float p1, float p2, int dir,
@@ -35,68 +35,93 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
   const int path = path_begin + w;
   const PathGeom g = sgm_path_geom(dir, path, H, W);
   if (g.mult == 0) return;
-  const bool accumulate = mode & kSgmAccumulate;
   const bool write_out = !(mode & kSgmNoOutput);
   const bool store_l = (mode & kSgmStoreL) && path == l_store_path;
-  const int dpad = NV * 32 * VW;
+  constexpr int dpad = NV * 32 * VW;
 
-  int x = g.sx, y = g.sy;
-  size_t pix = (size_t)y * W + x;
-  LaneVec<NV, VW> L, c_next;
-  lv_load<NV, VW, true>(L, cost + pix * D, lane, D);
-  float prev_intensity = image[pix];
+  // Pixel i of the path sits at pix0 + i*step: addresses are known up front, so the cost
+  // vector, the output vector (for the read-modify-write) and the intensity of the next
+  // PF pixels are kept in flight in registers while the recurrence runs.  The loop runs
+  // whole groups of PF pixels: prefetches past the end are clamped to the last pixel and
+  // the surplus steps are computed but not stored (branch-free steady state).
+  constexpr int PF = (NV * VW <= 4) ? 8 : ((NV * VW <= 6) ? 5 : 4);
+  const LaneCtx cx = lv_ctx<NV, VW>(lane, min_limit);
+  const long long pix0 = (long long)g.sy * W + g.sx;
+  const long long step = (long long)g.dy * W + g.dx;
+  const long long step_d = step * D;
+  const int n = g.n;
+  const int lane_off = lane * VW;
 
-  for (int i = 0; i < g.n; ++i) {
-    // prefetch the next pixel's cost vector and intensity
-    const bool has_next = i + 1 < g.n;
-    const int xn = x + g.dx, yn = y + g.dy;
-    const size_t pix_next = has_next ? (size_t)yn * W + xn : pix;
-    float intensity_next = 0.f;
-    if (has_next) {
-      lv_load<NV, VW, true>(c_next, cost + pix_next * D, lane, D);
-      intensity_next = image[pix_next];
-    }
+  // all pointers are pre-offset by the lane's first disparity
+  const float *cfetch = cost + pix0 * D + lane_off;
+  const float *sfetch = out + pix0 * D + lane_off;
+  const float *ifetch = image + pix0;
+  float *optr = out + pix0 * D + lane_off;
+  float *lptr = l_store + lane_off;
+  const int dl = D - lane_off;  // lv_load/lv_store bound relative to the lane offset
 
-    // out[pix] (+)= L
-    if (write_out) {
+  // step 0: L = C[p0]
+  LaneVec<NV, VW> L;
+  lv_load<NV, VW, true>(L, cfetch, 0, dl);
+  float prev_intensity = __ldg(ifetch);
+  if (write_out) {
+    if (ACC) {
       LaneVec<NV, VW> o;
-      float *optr = out + pix * D;
-      if (accumulate) {
-        lv_load<NV, VW, true>(o, optr, lane, D);
-#pragma unroll
-        for (int k = 0; k < NV; ++k)
-#pragma unroll
-          for (int j = 0; j < VW; ++j) o.v[k][j] += L.v[k][j];
-        lv_store<NV, VW, true>(o, optr, lane, D);
-      } else {
-        lv_store<NV, VW, true>(L, optr, lane, D);
-      }
-    }
-    if (store_l) lv_store<NV, VW, false>(L, l_store + (size_t)i * dpad, lane, dpad);
-
-    if (has_next) {
-      const float m = lv_min<NV, VW>(L, lane, min_limit);
-      LaneVec<NV, VW> lo, hi;
-      lv_neighbours<NV, VW>(L, lo, hi, lane);
-      const float q = p2 / fabsf(intensity_next - prev_intensity);
-      const float p2_adj = (p1 < q) ? q : p1;
-      const float far = m + p2_adj;
+      lv_load<NV, VW, true>(o, sfetch, 0, dl);
 #pragma unroll
       for (int k = 0; k < NV; ++k)
 #pragma unroll
-        for (int j = 0; j < VW; ++j) {
-          float best = L.v[k][j];
-          const float a = lo.v[k][j] + p1;
-          if (a < best) best = a;
-          const float b = hi.v[k][j] + p1;
-          if (b < best) best = b;
-          if (far < best) best = far;
-          L.v[k][j] = __fsub_rn(__fadd_rn(c_next.v[k][j], best), m);
+        for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+      lv_store<NV, VW, true>(o, optr, 0, dl);
+    } else {
+      lv_store<NV, VW, true>(L, optr, 0, dl);
+    }
+  }
+  if (store_l) lv_store<NV, VW, false>(L, lptr, 0, dpad);
+  if (n == 1) return;
+
+  // prologue: pixels 1..PF in flight
+  LaneVec<NV, VW> cbuf[PF], sbuf[PF];
+  float ibuf[PF];
+  int left = n - 1;  // pixels not yet fetched (beyond the current fetch pointer)
+#pragma unroll
+  for (int u = 0; u < PF; ++u) {
+    if (left > 0) { cfetch += step_d; sfetch += step_d; ifetch += step; --left; }
+    lv_load<NV, VW, true>(cbuf[u], cfetch, 0, dl);
+    if (ACC) lv_load<NV, VW, true>(sbuf[u], sfetch, 0, dl);
+    ibuf[u] = __ldg(ifetch);
+  }
+
+  for (int i = 1; i < n; i += PF) {
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+      const LaneVec<NV, VW> c = cbuf[u];
+      LaneVec<NV, VW> o;
+      if (ACC) o = sbuf[u];
+      const float intensity = ibuf[u];
+      // refill slot u with pixel i+u+PF (clamped)
+      if (left > 0) { cfetch += step_d; sfetch += step_d; ifetch += step; --left; }
+      lv_load<NV, VW, true>(cbuf[u], cfetch, 0, dl);
+      if (ACC) lv_load<NV, VW, true>(sbuf[u], sfetch, 0, dl);
+      ibuf[u] = __ldg(ifetch);
+
+      lv_sgm_step<NV, VW>(L, c, p1, sgm_p2_adjusted(p1, p2, intensity, prev_intensity), cx);
+      prev_intensity = intensity;
+      const bool live = i + u < n;
+      optr += step_d;
+      lptr += dpad;
+      if (live && write_out) {
+        if (ACC) {
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+#pragma unroll
+            for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+          lv_store<NV, VW, true>(o, optr, 0, dl);
+        } else {
+          lv_store<NV, VW, true>(L, optr, 0, dl);
         }
-      prev_intensity = intensity_next;
-      x = xn;
-      y = yn;
-      pix = pix_next;
+      }
+      if (live && store_l) lv_store<NV, VW, false>(L, lptr, 0, dpad);
     }
   }
 }
@@ -123,9 +148,14 @@ static int run_direction(const float *cost, const float *image, float *out, int 
                          cudaStream_t stream) {
   const int warps = 4;
   const int blocks = (path_count + warps - 1) / warps;
-  sgm_path_kernel<NV, VW><<<blocks, warps * 32, 0, stream>>>(
-      cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
-      l_store_path);
+  if (mode & kSgmAccumulate)
+    sgm_path_kernel<NV, VW, true><<<blocks, warps * 32, 0, stream>>>(
+        cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
+        l_store_path);
+  else
+    sgm_path_kernel<NV, VW, false><<<blocks, warps * 32, 0, stream>>>(
+        cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
+        l_store_path);
   return check_launch("sgm_path_kernel");
 }
 
