@@ -60,6 +60,14 @@ def build(reference: Path, force: bool = False, verbose: bool = True) -> Path | 
 
     build_dir = OUT_DIR / "build"
     build_dir.mkdir(parents=True, exist_ok=True)
+    # torch's cpp_extension serialises builds with a `lock` file and waits on it forever; a
+    # build that was killed leaves it behind and every later build() would hang.  This is the
+    # only builder of this directory (tests never build, they only check ref_ops.available()),
+    # so a lock found here is stale.
+    stale = build_dir / "lock"
+    if stale.exists():
+        print(f"[build_ref] removing stale {stale} left by an interrupted build", file=sys.stderr)
+        stale.unlink()
     load(
         name="_cstereomatch",
         sources=[str(reference / s) for s in SOURCES],
