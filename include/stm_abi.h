@@ -43,6 +43,10 @@ extern "C" {
                                 instead of k in [0, D-2] (compiled CPU reference,
                                 src/bordered_buffer.hpp:26-27) */
 #define STM_SGM_OVERWRITE 2u /* out = sum (skip the caller's zero fill) instead of out += sum */
+#define STM_SGM_REFERENCE_ORDER 4u /* one kernel per direction, adding into `out` in the reference's
+                                      direction order (slow: ~92 B/pix-disp of HBM traffic).  Default
+                                      is two fused raster sweeps (~20 B/pix-disp) whose fp32 sums
+                                      associate differently (same values within a few ulp). */
 
 /* flags of stm_dp_f32 */
 #define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68);

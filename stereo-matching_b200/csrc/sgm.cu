@@ -159,8 +159,8 @@ static int run_direction(const float *cost, const float *image, float *out, int 
   return check_launch("sgm_path_kernel");
 }
 
-static int repeat_add(float *out, float *l_store, int H, int W, int D, int dpad, int dir,
-                      int path, int times, cudaStream_t stream) {
+int sgm_repeat_add(float *out, float *l_store, int H, int W, int D, int dpad, int dir, int path,
+                   int times, cudaStream_t stream) {
   const PathGeom g = sgm_path_geom(dir, path, H, W);
   const int total = g.n * D;
   sgm_repeat_add_kernel<<<(total + 255) / 256, 256, 0, stream>>>(out, l_store, W, D, dpad, g.sx,
@@ -193,7 +193,7 @@ static int sgm_by_direction(const float *cost, const float *image, float *out, i
                                mode | kSgmStoreL, ws, multi, stream);
     if (rc) return rc;
     if (times > 0) {
-      rc = repeat_add(out, ws, H, W, D, dpad, dir, multi, times, stream);
+      rc = sgm_repeat_add(out, ws, H, W, D, dpad, dir, multi, times, stream);
       if (rc) return rc;
     }
   }
@@ -222,7 +222,7 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
         rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 5, multi, 1, min_limit,
                                    kSgmNoOutput | kSgmStoreL, ws, multi, stream);
         if (rc) return rc;
-        rc = repeat_add(out, ws, H, W, D, dpad, 5, multi, times, stream);
+        rc = sgm_repeat_add(out, ws, H, W, D, dpad, 5, multi, times, stream);
         if (rc) return rc;
       }
     }
@@ -233,10 +233,20 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
   return STM_OK;
 }
 
-size_t sgm_workspace_bytes(int H, int W, int D) {
+// sgm_sweep.cu
+size_t sgm_sweep_workspace_bytes(int H, int W, int D);
+int launch_sgm_sweeps(const float *, const float *, float *, int, int, int, float, float, unsigned,
+                      void *, size_t, cudaStream_t);
+
+static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
   const LaneMap m = pick_lane_map(D);
   const size_t dpad = (size_t)m.NV * 32 * m.VW;
   return (size_t)(H < W ? H : W) * dpad * sizeof(float);
+}
+
+size_t sgm_workspace_bytes(int H, int W, int D) {
+  const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_sweep_workspace_bytes(H, W, D);
+  return a > b ? a : b;
 }
 
 int launch_sgm(const float *cost, const float *image, float *out, int H, int W, int D, float p1,
@@ -248,6 +258,12 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   if (workspace_bytes < sgm_workspace_bytes(H, W, D) || (workspace == nullptr && H != W))
     return fail(STM_EINVAL, "sgm: workspace too small (%zu < %zu)", workspace_bytes,
                 sgm_workspace_bytes(H, W, D));
+  if (!(flags & STM_SGM_REFERENCE_ORDER)) {
+    // default: two fused raster sweeps (sgm_sweep.cu); 1 = shape not handled there
+    const int rc = launch_sgm_sweeps(cost, image, out, H, W, D, p1, p2, flags, workspace,
+                                     workspace_bytes, stream);
+    if (rc != 1) return rc;
+  }
   const LaneMap m = pick_lane_map(D);
   float *ws = static_cast<float *>(workspace);
 #define STM_SGM_CASE(NV_, VW_)                                                            \

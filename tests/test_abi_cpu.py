@@ -39,8 +39,16 @@ def test_version_and_error_strings():
 def test_workspace_query_is_pure():
     lib = ctypes.CDLL(str(LIB))
     lib.stm_sgm_workspace_bytes.restype = ctypes.c_size_t
-    assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == 1080 * 128 * 4
-    assert lib.stm_sgm_workspace_bytes(30, 18, 16) == 18 * 32 * 4
+
+    def expect(H, W, dpad):
+        # csrc/sgm_sweep.cu: [l-store dir 5][l-store dir 7][CTA->CTA rings: ceil(H/4) x 32 slots
+        # x 3 vectors][flags: 2 sweeps x {gprog, gcons} x ceil(H/4)], each 16-byte aligned
+        a16 = lambda n: (n + 15) // 16 * 16
+        g = (H + 3) // 4
+        return 2 * a16(min(H, W) * dpad * 4) + a16(g * 32 * 3 * dpad * 4) + a16(4 * g * 4)
+
+    assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == expect(1080, 1920, 128)
+    assert lib.stm_sgm_workspace_bytes(30, 18, 16) == expect(30, 18, 32)  # D=16 pads to 32 lanes
     assert lib.stm_sgm_workspace_bytes(0, 0, 0) == 0
 
 

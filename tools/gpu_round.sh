@@ -10,8 +10,13 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O
 
 echo "== pytest -m gpu"
 timeout 900 python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest.log 2>&1
-echo "pytest exit=$?" | tee -a $OUT/${TAG}_pytest.log
-tail -5 $OUT/${TAG}_pytest.log
+PYTEST_RC=$?
+echo "pytest exit=$PYTEST_RC" >> $OUT/${TAG}_pytest.log
+tail -25 $OUT/${TAG}_pytest.log
+if [ $PYTEST_RC -ne 0 ]; then
+  echo "parity tests failed: skipping benches and ncu (never profile a faulting program)"
+  exit $PYTEST_RC
+fi
 
 echo "== stage bench"
 timeout 300 python tools/stage_bench.py 1080 1920 128 > $OUT/${TAG}_stages_1080p_d128.json 2> $OUT/${TAG}_stages.err
