@@ -43,10 +43,11 @@ extern "C" {
                                 instead of k in [0, D-2] (compiled CPU reference,
                                 src/bordered_buffer.hpp:26-27) */
 #define STM_SGM_OVERWRITE 2u /* out = sum (skip the caller's zero fill) instead of out += sum */
-#define STM_SGM_REFERENCE_ORDER 4u /* one kernel per direction, adding into `out` in the reference's
-                                      direction order (slow: ~92 B/pix-disp of HBM traffic).  Default
-                                      is two fused raster sweeps (~20 B/pix-disp) whose fp32 sums
-                                      associate differently (same values within a few ulp). */
+#define STM_SGM_FUSED_SWEEPS 4u /* EXPERIMENTAL: two fused raster sweeps (csrc/sgm_sweep.cu) instead of
+                                   one kernel per direction.  Moves ~20 instead of ~92 B/pix-disp of
+                                   HBM traffic and passes the same parity tests, but is latency-bound
+                                   and currently ~5x SLOWER (profiles/r01_v3_fused_sweeps.md).  fp32
+                                   sums associate differently (same values within a few ulp). */
 
 /* flags of stm_dp_f32 */
 #define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68);

@@ -101,7 +101,7 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
   if (rc) return rc;
   STM_REQUIRE(cost && left && out, "sgm: null pointer");
   STM_REQUIRE(cost != out, "sgm: output must not alias the cost volume");
-  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_REFERENCE_ORDER)) == 0, "sgm: unknown flags 0x%x",
+  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_FUSED_SWEEPS)) == 0, "sgm: unknown flags 0x%x",
               flags);
   if ((rc = require_device())) return rc;
   return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace,

@@ -258,8 +258,8 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   if (workspace_bytes < sgm_workspace_bytes(H, W, D) || (workspace == nullptr && H != W))
     return fail(STM_EINVAL, "sgm: workspace too small (%zu < %zu)", workspace_bytes,
                 sgm_workspace_bytes(H, W, D));
-  if (!(flags & STM_SGM_REFERENCE_ORDER)) {
-    // default: two fused raster sweeps (sgm_sweep.cu); 1 = shape not handled there
+  if (flags & STM_SGM_FUSED_SWEEPS) {
+    // opt-in: two fused raster sweeps (sgm_sweep.cu); 1 = shape not handled there
     const int rc = launch_sgm_sweeps(cost, image, out, H, W, D, p1, p2, flags, workspace,
                                      workspace_bytes, stream);
     if (rc != 1) return rc;

@@ -1,7 +1,11 @@
 // sgm_sweep.cu -- semiglobal aggregation as TWO fused raster sweeps (sm_100a).
 //
 // Replaces AggregationOps::RunSemiglobal (reference src/semiglobal.cpp:167-197; recurrence
-// SGMCostOperator::operator(), :116-159) for the default mode of stm_sgm_f32.  The
+// SGMCostOperator::operator(), :116-159) when stm_sgm_f32 is given STM_SGM_FUSED_SWEEPS.
+// EXPERIMENTAL: correct (same parity tests as the default path) and it does cut HBM traffic to
+// the designed 19.7 B/pix-disp (ncu), but with one warp per image row the wavefront is
+// latency-bound: ~420 ns per pixel step and ~19 pixels of lag per row at 1080p, 20.6 ms per
+// frame against 4.3 ms for the per-direction kernels (profiles/r01_v3_fused_sweeps.md).  The
 // per-direction kernels in sgm.cu move ~92 B per pixel-disparity (8 x read C, read S,
 // write S); here the forward sweep computes -> v \v /v for every pixel in one pass and the
 // backward sweep <- ^ ^\ ^/ in a second one: read C twice, write S, read+write S = 20 B.
@@ -28,7 +32,7 @@
 //
 // Summation order differs from the reference's (it adds direction after direction); all
 // terms are non-negative, so the result stays within a few ulp (bar: 1e-4 relative).
-// STM_SGM_REFERENCE_ORDER selects the per-direction kernels instead.
+// The default mode of stm_sgm_f32 is the per-direction kernels of sgm.cu.
 #include <cooperative_groups.h>
 
 #include "lanevec.cuh"
@@ -57,15 +61,26 @@ struct SweepParams {
   int c_sx, e_sx;   // x of the first pixel of those paths
 };
 
-// ---- acquire / release flags ----------------------------------------------------------
-__device__ __forceinline__ unsigned ld_acquire_smem(const unsigned *p) {
+// ---- progress flags ---------------------------------------------------------------------
+// Shared-memory flags (row -> row inside a CTA) are STRONG RELAXED accesses, i.e. plain
+// LDS/STS with no fence.  st.release.cta would compile to MEMBAR.ALL.CTA + STS, and that
+// barrier waits for every earlier memory operation of the thread -- including the global
+// prefetch loads a compute warp keeps in flight -- which costs one DRAM round trip per
+// pixel (measured: 28 ms instead of ~4 ms per frame).  Ordering of "data, then flag" relies
+// on (a) __syncwarp() between the lanes' data stores and lane 0's flag store, (b) the "memory"
+// clobbers (compiler order), and (c) the SM performing one warp's shared-memory requests in
+// issue order through its single shared-memory pipeline: a reader that sees the new flag
+// value therefore sees the data stored before it.  (c) is a property of the hardware, not
+// of the PTX memory model; the GPU parity tests (bit-identical reruns included) guard it.
+// Global-memory flags (CTA -> CTA, helper warps only) use real acquire/release at gpu scope.
+__device__ __forceinline__ unsigned ld_flag_smem(const unsigned *p) {
   unsigned v;
-  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];"
+  asm volatile("ld.relaxed.cta.shared.u32 %0, [%1];"
                : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_smem(unsigned *p, unsigned v) {
-  asm volatile("st.release.cta.shared.u32 [%0], %1;"
+__device__ __forceinline__ void st_flag_smem(unsigned *p, unsigned v) {
+  asm volatile("st.relaxed.cta.shared.u32 [%0], %1;"
                :: "r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
 }
 __device__ __forceinline__ unsigned ld_acquire_gmem(const unsigned *p) {
@@ -78,17 +93,25 @@ __device__ __forceinline__ void st_release_gmem(unsigned *p, unsigned v) {
 }
 
 // Waits until *flag >= need; returns the value seen.  Bounded: a protocol bug traps
-// (loud launch failure) instead of hanging the GPU.
-__device__ __forceinline__ unsigned wait_smem(const unsigned *flag, unsigned need) {
-  unsigned v = ld_acquire_smem(flag);
-  unsigned tries = 0, ns = 20;
+// (loud launch failure) instead of hanging the GPU.  Short waits (the steady state of the
+// wavefront) poll back to back; only long ones (a row waiting for the wavefront to arrive)
+// sleep.
+__device__ __noinline__ unsigned wait_smem_slow(const unsigned *flag, unsigned need) {
+  unsigned v = ld_flag_smem(flag);
+  unsigned tries = 0, ns = 32;
   while (v < need) {
-    __nanosleep(ns);
-    if (ns < 256) ns <<= 1;
-    v = ld_acquire_smem(flag);
-    if (++tries > kSpinCap) __trap();
+    if (++tries > 64) {
+      __nanosleep(ns);
+      if (ns < 512) ns <<= 1;
+      if (tries > kSpinCap) __trap();
+    }
+    v = ld_flag_smem(flag);
   }
   return v;
+}
+__device__ __forceinline__ unsigned wait_smem(const unsigned *flag, unsigned need) {
+  const unsigned v = ld_flag_smem(flag);
+  return v >= need ? v : wait_smem_slow(flag, need);
 }
 __device__ __forceinline__ unsigned wait_gmem(const unsigned *flag, unsigned need) {
   unsigned v = ld_acquire_gmem(flag);
@@ -155,7 +178,7 @@ __device__ void sweep_importer(float *smem, const SweepParams &P, int cta, int l
     cp_async_wait_all();
     __syncwarp();
     if (lane == 0) {
-      st_release_smem(prog0, limit);
+      st_flag_smem(prog0, limit);
       st_release_gmem(gcons, limit);
     }
     done = limit;
@@ -188,7 +211,7 @@ __device__ void sweep_exporter(float *smem, const SweepParams &P, int cta, int l
     }
     __syncwarp();
     if (lane == 0) {
-      st_release_smem(consR, limit);  // the shared slots may be overwritten
+      st_flag_smem(consR, limit);     // the shared slots may be overwritten
       st_release_gmem(gprog, limit);  // ... and the global ones may be read
     }
     done = limit;
@@ -290,91 +313,118 @@ sgm_sweep_kernel(const SweepParams P) {
   if (has_above) {  // vectors of the row above for lx = 0: pixels 0 and 1
     seen_prog = wait_smem(prog_in, W < 2 ? W : 2);
     lv_load<NV, VW, false>(aB, ring_in, 0, DPAD);
-    if (W > 1) lv_load<NV, VW, false>(aE, ring_in + (1 & mask_in) * S::kSlot + 2 * DPAD, 0, DPAD);
+    lv_load<NV, VW, false>(aE, ring_in + ((W > 1 ? 1 : 0) & mask_in) * S::kSlot + 2 * DPAD, 0, DPAD);
   }
   float bA = 0.f, bB = 0.f, bC = 0.f, bE = 0.f;  // lane l: adaptive P2 of pixel (lx & ~31) + l
 
-  for (int lx0 = 0; lx0 < W; lx0 += PF) {
-    if ((lx0 & 31) == 0) {
-      int q = lx0 + lane;
-      if (q > W - 1) q = W - 1;
-      const int ql = q > 0 ? q - 1 : 0, qr = q < W - 1 ? q + 1 : W - 1;
-      const float i0 = __ldg(irow + phys(q));
-      bA = sgm_p2_adjusted(p1, p2, i0, __ldg(irow + phys(ql)));
-      bB = sgm_p2_adjusted(p1, p2, i0, __ldg(irow_a + phys(q)));
-      bC = sgm_p2_adjusted(p1, p2, i0, __ldg(irow_a + phys(ql)));
-      bE = sgm_p2_adjusted(p1, p2, i0, __ldg(irow_a + phys(qr)));
+  // adaptive penalties of 32 consecutive pixels, one pixel per lane (4 divisions per lane per
+  // 32 pixels instead of 4 per pixel); broadcast by shuffle in step()
+  auto penalties = [&](int lx0) {
+    int q = lx0 + lane;
+    if (q > W - 1) q = W - 1;
+    const int ql = q > 0 ? q - 1 : 0, qr = q < W - 1 ? q + 1 : W - 1;
+    const float i0 = __ldg(irow + phys(q));
+    bA = sgm_p2_adjusted(p1, p2, i0, __ldg(irow + phys(ql)));
+    bB = sgm_p2_adjusted(p1, p2, i0, __ldg(irow_a + phys(q)));
+    bC = sgm_p2_adjusted(p1, p2, i0, __ldg(irow_a + phys(ql)));
+    bE = sgm_p2_adjusted(p1, p2, i0, __ldg(irow_a + phys(qr)));
+  };
+
+  // One pixel.  Every load whose latency matters is issued UNCONDITIONALLY (clamped indices):
+  // a load under a branch makes the compiler load into a temporary and copy at the join,
+  // i.e. wait for it at once (that cost 5x in the first version of this kernel).
+  auto step = [&](const int lx, const Vec &c, Vec acc) {
+    // vectors of the row above for step lx+1: pixels lx, lx+1, lx+2 (row 0 reads unused smem)
+    Vec nB, nC, nE;
+    {
+      const int l1 = lx + 1 < W ? lx + 1 : W - 1, l2 = lx + 2 < W ? lx + 2 : W - 1;
+      const unsigned need = has_above ? (unsigned)(lx + 3 < W ? lx + 3 : W) : 0u;
+      if (seen_prog < need) seen_prog = wait_smem(prog_in, need);
+      lv_load<NV, VW, false>(nB, ring_in + (l1 & mask_in) * S::kSlot, 0, DPAD);
+      lv_load<NV, VW, false>(nC, ring_in + (lx & mask_in) * S::kSlot + DPAD, 0, DPAD);
+      lv_load<NV, VW, false>(nE, ring_in + (l2 & mask_in) * S::kSlot + 2 * DPAD, 0, DPAD);
     }
+    const int bl = lx & 31;
+    const float pA = __shfl_sync(FULL, bA, bl), pB = __shfl_sync(FULL, bB, bl);
+    const float pC = __shfl_sync(FULL, bC, bl), pE = __shfl_sync(FULL, bE, bl);
+
+    // four recurrences; a path that STARTS at this pixel takes L = C (select, no branch)
+    Vec LB = aB, LC = aC, LE = aE;
+    lv_sgm_step<NV, VW>(LA, c, p1, pA, cx);
+    lv_sgm_step<NV, VW>(LB, c, p1, pB, cx);
+    lv_sgm_step<NV, VW>(LC, c, p1, pC, cx);
+    lv_sgm_step<NV, VW>(LE, c, p1, pE, cx);
+    const bool sA = lx == 0, sB = !has_above, sC = !has_above || lx == 0,
+               sE = !has_above || lx == W - 1;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int j = 0; j < VW; ++j) {
+        LA.v[k][j] = sA ? c.v[k][j] : LA.v[k][j];
+        LB.v[k][j] = sB ? c.v[k][j] : LB.v[k][j];
+        LC.v[k][j] = sC ? c.v[k][j] : LC.v[k][j];
+        LE.v[k][j] = sE ? c.v[k][j] : LE.v[k][j];
+      }
+
+    // out (+)= A + B + C + E, one fp32 addition per direction like the reference
+    if (ACC) lv_add<NV, VW>(acc, LA); else acc = LA;
+    lv_add<NV, VW>(acc, LB);
+    if (BACKWARD) {
+      const int x = W - 1 - lx;
+      const int mc = sweep_mult_dir5(x, y, H, W), me = sweep_mult_dir7(x, y, H, W);
+      if (mc) lv_add<NV, VW>(acc, LC);
+      if (me) lv_add<NV, VW>(acc, LE);
+      if (mc > 1 && P.lstore_c)
+        lv_store<NV, VW, false>(LC, P.lstore_c + (size_t)(P.c_sx - x) * DPAD + lane_off, 0, DPAD);
+      if (me > 1 && P.lstore_e)
+        lv_store<NV, VW, false>(LE, P.lstore_e + (size_t)(x - P.e_sx) * DPAD + lane_off, 0, DPAD);
+    } else {
+      lv_add<NV, VW>(acc, LC);
+      lv_add<NV, VW>(acc, LE);
+    }
+    lv_store<NV, VW, true>(acc, orow + (long long)lx * stepd, 0, dl);
+
+    if (has_below) {  // hand this pixel's downward-looking vectors to the next row
+      const unsigned need = lx >= kRingK ? (unsigned)(lx - kRingK + 1) : 0u;
+      if (seen_cons < need) seen_cons = wait_smem(cons_out, need);
+      float *slot = ring_out + (lx & (kRingK - 1)) * S::kSlot;
+      lv_store<NV, VW, false>(LB, slot, 0, DPAD);
+      lv_store<NV, VW, false>(LC, slot + DPAD, 0, DPAD);
+      lv_store<NV, VW, false>(LE, slot + 2 * DPAD, 0, DPAD);
+    }
+    __syncwarp();
+    if (lane == 0) {
+      if (has_below) st_flag_smem(prog_out, lx + 1);
+      if (has_above) st_flag_smem(cons_in, lx + 1);
+    }
+    aB = nB; aC = nC; aE = nE;
+  };
+
+  // full groups of PF pixels: branch-free, the refill loads run PF pixels ahead
+  int lx = 0;
+  for (int g = W / PF; g > 0; --g) {
+    if ((lx & 31) == 0) penalties(lx);
 #pragma unroll
     for (int u = 0; u < PF; ++u) {
-      const int lx = lx0 + u;
-      if (lx < W) {  // warp-uniform
-        const Vec c = cbuf[u];
-        Vec acc;
-        if (ACC) acc = sbuf[u];
-        {  // refill slot u with pixel lx + PF (clamped to the row)
-          const int f = lx + PF < W ? lx + PF : W - 1;
-          lv_load<NV, VW, true>(cbuf[u], crow + (long long)f * stepd, 0, dl);
-          if (ACC) lv_load<NV, VW, true>(sbuf[u], orow + (long long)f * stepd, 0, dl);
-        }
-        // above vectors of step lx+1 (pixels lx, lx+1, lx+2 of the row above)
-        Vec nB = aB, nC = aC, nE = aE;
-        if (has_above && lx + 1 < W) {
-          const unsigned need = lx + 3 < W ? lx + 3 : W;
-          if (seen_prog < need) seen_prog = wait_smem(prog_in, need);
-          lv_load<NV, VW, false>(nB, ring_in + ((lx + 1) & mask_in) * S::kSlot, 0, DPAD);
-          lv_load<NV, VW, false>(nC, ring_in + (lx & mask_in) * S::kSlot + DPAD, 0, DPAD);
-          if (lx + 2 < W)
-            lv_load<NV, VW, false>(nE, ring_in + ((lx + 2) & mask_in) * S::kSlot + 2 * DPAD, 0, DPAD);
-        }
-        const int bl = lx & 31;
-        const float pA = __shfl_sync(FULL, bA, bl), pB = __shfl_sync(FULL, bB, bl);
-        const float pC = __shfl_sync(FULL, bC, bl), pE = __shfl_sync(FULL, bE, bl);
-
-        if (lx == 0) LA = c; else lv_sgm_step<NV, VW>(LA, c, p1, pA, cx);
-        Vec LB = c, LC = c, LE = c;
-        if (has_above) {
-          LB = aB;
-          lv_sgm_step<NV, VW>(LB, c, p1, pB, cx);
-          if (lx > 0) { LC = aC; lv_sgm_step<NV, VW>(LC, c, p1, pC, cx); }
-          if (lx < W - 1) { LE = aE; lv_sgm_step<NV, VW>(LE, c, p1, pE, cx); }
-        }
-
-        // out (+)= A + B + C + E, one fp32 addition per direction like the reference
-        if (ACC) lv_add<NV, VW>(acc, LA); else acc = LA;
-        lv_add<NV, VW>(acc, LB);
-        if (BACKWARD) {
-          const int x = W - 1 - lx;
-          const int mc = sweep_mult_dir5(x, y, H, W), me = sweep_mult_dir7(x, y, H, W);
-          if (mc) lv_add<NV, VW>(acc, LC);
-          if (me) lv_add<NV, VW>(acc, LE);
-          if (mc > 1 && P.lstore_c)
-            lv_store<NV, VW, false>(LC, P.lstore_c + (size_t)(P.c_sx - x) * DPAD + lane_off, 0, DPAD);
-          if (me > 1 && P.lstore_e)
-            lv_store<NV, VW, false>(LE, P.lstore_e + (size_t)(x - P.e_sx) * DPAD + lane_off, 0, DPAD);
-        } else {
-          lv_add<NV, VW>(acc, LC);
-          lv_add<NV, VW>(acc, LE);
-        }
-        lv_store<NV, VW, true>(acc, orow + (long long)lx * stepd, 0, dl);
-
-        if (has_below) {  // hand this pixel's downward-looking vectors to the next row
-          if (lx >= kRingK) {
-            const unsigned need = lx - kRingK + 1;
-            if (seen_cons < need) seen_cons = wait_smem(cons_out, need);
-          }
-          float *slot = ring_out + (lx & (kRingK - 1)) * S::kSlot;
-          lv_store<NV, VW, false>(LB, slot, 0, DPAD);
-          lv_store<NV, VW, false>(LC, slot + DPAD, 0, DPAD);
-          lv_store<NV, VW, false>(LE, slot + 2 * DPAD, 0, DPAD);
-        }
-        __syncwarp();
-        if (lane == 0) {
-          if (has_below) st_release_smem(prog_out, lx + 1);
-          if (has_above) st_release_smem(cons_in, lx + 1);
-        }
-        aB = nB; aC = nC; aE = nE;
-      }
+      const Vec c = cbuf[u];
+      Vec acc = c;
+      if (ACC) acc = sbuf[u];
+      const long long off = (long long)(lx + PF < W ? lx + PF : W - 1) * stepd;
+      lv_load<NV, VW, true>(cbuf[u], crow + off, 0, dl);
+      if (ACC) lv_load<NV, VW, true>(sbuf[u], orow + off, 0, dl);
+      step(lx, c, acc);
+      ++lx;
+    }
+  }
+  // tail: fewer than PF pixels, already sitting in cbuf / sbuf
+  if (lx < W && (lx & 31) == 0) penalties(lx);
+#pragma unroll
+  for (int u = 0; u < PF; ++u) {
+    if (lx < W) {
+      Vec acc = cbuf[u];
+      if (ACC) acc = sbuf[u];
+      step(lx, cbuf[u], acc);
+      ++lx;
     }
   }
 }

@@ -4,7 +4,7 @@ from typing import Optional
 import torch
 
 from ._common import empty_tensor
-from ._cstereomatch import STM_SGM_MIN_ALL_D, STM_SGM_OVERWRITE, STM_SGM_REFERENCE_ORDER
+from ._cstereomatch import STM_SGM_MIN_ALL_D, STM_SGM_OVERWRITE, STM_SGM_FUSED_SWEEPS
 from ._cstereomatch import AggregationOps as _AggregationOps
 
 
@@ -17,17 +17,18 @@ class Semiglobal:
     min_over_all_d=False keeps the compiled CPU reference's min over d in [0, D-2]
     (SURVEY F6); True takes the min over all D like the reference CUDA kernel.
     Unlike the reference's CUDA branch, D does not have to be a power of two.
-    reference_order=True runs one kernel per direction and adds the eight directions into
-    the output in the reference's order (about 4x slower); the default fuses them into two
-    raster sweeps whose fp32 sums associate differently (same values within a few ulp).
+    The default runs one kernel per direction and adds the eight directions into the output
+    in the reference's order.  fused_sweeps=True (experimental) computes them in two raster
+    sweeps: a quarter of the HBM traffic and the same values within a few ulp, but it is
+    latency-bound and currently about 5x slower.
     """
 
     def __init__(self, penalty1: float = 0.1, penalty2: float = 0.2, *,
-                 min_over_all_d: bool = False, reference_order: bool = False):
+                 min_over_all_d: bool = False, fused_sweeps: bool = False):
         self.penalty1 = penalty1
         self.penalty2 = penalty2
         self.min_over_all_d = min_over_all_d
-        self.reference_order = reference_order
+        self.fused_sweeps = fused_sweeps
 
     def __call__(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
                  sga_volume: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -37,8 +38,8 @@ class Semiglobal:
         sga_volume = empty_tensor(*cost_volume.size(), dtype=cost_volume.dtype,
                                   device=cost_volume.device, reuse_tensor=sga_volume)
         flags = STM_SGM_OVERWRITE | (STM_SGM_MIN_ALL_D if self.min_over_all_d else 0)
-        if self.reference_order:
-            flags |= STM_SGM_REFERENCE_ORDER
+        if self.fused_sweeps:
+            flags |= STM_SGM_FUSED_SWEEPS
         _AggregationOps.run_semiglobal(cost_volume, left_image, self.penalty1, self.penalty2,
                                        sga_volume, flags)
         return sga_volume

@@ -113,14 +113,14 @@ def test_sgm_golden(sm, golden, case):
     (35, 13, 96, "unit", 0.3, 1.0, True), (11, 29, 20, "raw", 5.0, 9.0, False),
     (1, 9, 32, "unit", 0.1, 0.2, False), (9, 1, 32, "unit", 0.1, 0.2, False),
 ])
-@pytest.mark.parametrize("reference_order", [False, True])
-def test_sgm_vs_oracle(sm, H, W, D, scale, p1, p2, all_d, reference_order):
-    """Both SGM modes: fused raster sweeps (default) and one kernel per direction."""
+@pytest.mark.parametrize("fused_sweeps", [False, True])
+def test_sgm_vs_oracle(sm, H, W, D, scale, p1, p2, all_d, fused_sweeps):
+    """Both SGM modes: one kernel per direction (default) and the fused raster sweeps."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 7 + W, scale=scale)
     cost = O.ssd(left, right, D, 3)
     want = O.sgm(cost, left, p1, p2, min_over_all_d=all_d)
     got = sm.aggregation.Semiglobal(p1, p2, min_over_all_d=all_d,
-                                    reference_order=reference_order)(cuda(cost), cuda(left))
+                                    fused_sweeps=fused_sweeps)(cuda(cost), cuda(left))
     assert_volume_close(got, want)
 
 
@@ -133,12 +133,13 @@ def test_sgm_sweeps_many_ctas_and_ring_wraps(sm, H, W, D):
     cost = O.ssd(left, right, D, 3)
     want = O.sgm(cost, left, 0.1, 0.2)
     l, c = cuda(left), cuda(cost)
-    got = sm.aggregation.Semiglobal()(c, l)
+    fused = sm.aggregation.Semiglobal(fused_sweeps=True)
+    got = fused(c, l)
     assert_volume_close(got, want)
     # deterministic: a second run is bit-identical
-    assert torch.equal(got, sm.aggregation.Semiglobal()(c, l))
+    assert torch.equal(got, fused(c, l))
     # and the two modes agree with each other to the same bar
-    assert_volume_close(sm.aggregation.Semiglobal(reference_order=True)(c, l), got.cpu().numpy())
+    assert_volume_close(sm.aggregation.Semiglobal()(c, l), got.cpu().numpy())
 
 
 def test_sgm_accumulates_like_the_reference(sm):
@@ -305,16 +306,18 @@ def test_full_size_1080p_properties(sm):
     assert bool(torch.equal(d1, d2)) and int(d1.min()) >= 0 and int(d1.max()) < D
 
 
-def test_full_height_sgm_column_strip_vs_oracle(sm):
+@pytest.mark.parametrize("fused_sweeps", [False, True])
+def test_full_height_sgm_column_strip_vs_oracle(sm, fused_sweeps):
     """Full-height (1080 rows), narrow strip: exercises long paths and the 1080-fold
-    corner-diagonal multiplicity against the oracle."""
+    corner-diagonal multiplicity against the oracle (270 CTAs in the fused-sweep mode)."""
     H, W, D = 1080, 24, 32
     left, right, _ = synth.random_dot_pair(H, W, D, seed=77, scale="unit")
     cost = O.ssd(left, right, D, 3)
-    got = sm.aggregation.Semiglobal()(cuda(cost), cuda(left))
+    sgm = sm.aggregation.Semiglobal(fused_sweeps=fused_sweeps)
+    got = sgm(cuda(cost), cuda(left))
     assert_volume_close(got, O.sgm(cost, left, 0.1, 0.2))
     H, W = 24, 1100
     left, right, _ = synth.random_dot_pair(H, W, D, seed=78, scale="unit")
     cost = O.ssd(left, right, D, 3)
-    got = sm.aggregation.Semiglobal()(cuda(cost), cuda(left))
+    got = sgm(cuda(cost), cuda(left))
     assert_volume_close(got, O.sgm(cost, left, 0.1, 0.2))
