@@ -95,10 +95,9 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(mhz)}
 
 
-def make_frames(n_frames: int, first_seed: int):
+def make_frames(seeds):
     from oracle import synth
-    return [synth.random_dot_pair(H, W, D, seed=first_seed + f, scale="raw")[:2]
-            for f in range(n_frames)]
+    return [synth.random_dot_pair(H, W, D, seed=s, scale="raw")[:2] for s in seeds]
 
 
 # ---------------------------------------------------------------------------------------
@@ -181,6 +180,7 @@ def run_b200_arm(args):
 
     import stereomatch
     from stereomatch import _cstereomatch as C
+    from stereomatch import sharding
 
     def barrier():
         if world > 1:
@@ -189,7 +189,7 @@ def run_b200_arm(args):
 
     F = args.frames
     # frame f of rank r: seed 1000 + r*F + f (frame-sharded batch, no collective)
-    host = make_frames(F, 1000 + rank * F)
+    host = make_frames(sharding.frame_seeds(1000, F, rank))
     pinned = [(torch.from_numpy(l).pin_memory(), torch.from_numpy(r).pin_memory()) for l, r in host]
     dev_frames = [(l.to(dev), r.to(dev)) for l, r in pinned]
     out_host = [torch.empty(H, W, dtype=torch.int32).pin_memory() for _ in range(F)]
@@ -218,10 +218,7 @@ def run_b200_arm(args):
         e1.record()
         barrier()
         t1 = time.perf_counter()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), t0, t1
+        return sharding.max_over_ranks(e0.elapsed_time(e1), dev), t0, t1
 
     for _ in range(args.warmup):
         step_resident()

@@ -6,6 +6,7 @@ namespace stm {
 int launch_ssd_generic(const float *, const float *, float *, int, int, int, int, cudaStream_t);
 int launch_birchfield_generic(const float *, const float *, float *, int, int, int, cudaStream_t);
 int launch_ssd_tiled(const float *, const float *, float *, int, int, int, int, cudaStream_t);
+int launch_birchfield_tiled(const float *, const float *, float *, int, int, int, cudaStream_t);
 
 int launch_ssd(const float *left, const float *right, float *cost, int H, int W, int D, int k,
                cudaStream_t stream) {
@@ -18,6 +19,10 @@ int launch_ssd(const float *left, const float *right, float *cost, int H, int W,
 
 int launch_birchfield(const float *left, const float *right, float *cost, int H, int W, int D,
                       cudaStream_t stream) {
+  // one CTA per scanline with the BT terms evaluated once (birchfield_tiled.cu); returns 1 for
+  // the shapes it does not cover (then the straightforward kernel runs instead)
+  const int rc = launch_birchfield_tiled(left, right, cost, H, W, D, stream);
+  if (rc != 1) return rc;
   return launch_birchfield_generic(left, right, cost, H, W, D, stream);
 }
 

@@ -81,13 +81,22 @@ def test_birchfield_golden_shift_relation(sm, golden, case):
         assert np.allclose(a, b, rtol=RTOL, atol=0)
 
 
-@pytest.mark.parametrize("H,W,D,scale", [(21, 45, 16, "raw"), (21, 45, 32, "unit"),
-                                           (12, 150, 128, "unit"), (30, 9, 64, "raw"),
-                                           (8, 70, 192, "unit")])
+@pytest.mark.parametrize("H,W,D,scale", [
+    (21, 45, 16, "raw"), (21, 45, 32, "unit"), (12, 150, 128, "unit"), (30, 9, 64, "raw"),
+    (8, 70, 192, "unit"),
+    (5, 7, 4, "unit"),        # W < 8: straightforward kernel
+    (6, 61, 160, "unit"),     # 5 lane groups: straightforward kernel
+    (4, 203, 256, "unit"),    # 8 lane groups, width not a multiple of 8
+    (9, 33, 20, "unit"), (3, 1000, 96, "raw"),
+    (4, 1920, 128, "unit"),   # 1080p scanlines: 46 KB of shared memory per CTA
+    (2, 2500, 64, "unit"),    # > 48 KB: opt-in shared memory
+])
 def test_birchfield_vs_oracle(sm, H, W, D, scale):
+    """Bit-exact for every input: the kernels keep the oracle's expressions and its
+    left-to-right tap order (taps outside [d, W) add an exact +0)."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=3 * H + W, scale=scale)
     got = sm.cost.Birchfield(D)(cuda(left), cuda(right))
-    assert_volume_close(got, O.birchfield(left, right, D), exact=(scale == "raw"))
+    assert_volume_close(got, O.birchfield(left, right, D), exact=True)
 
 
 # -------------------------------------------------------------------------------- SGM
