@@ -43,7 +43,7 @@ extern "C" {
                                 instead of k in [0, D-2] (compiled CPU reference,
                                 src/bordered_buffer.hpp:26-27) */
 #define STM_SGM_OVERWRITE 2u /* out = sum (skip the caller's zero fill) instead of out += sum */
-#define STM_SGM_FUSED_SWEEPS 4u /* EXPERIMENTAL: two fused raster sweeps (csrc/sgm_sweep.cu) instead of
+#define STM_SGM_FUSED_SWEEPS 4u /* EXPERIMENTAL: two fused raster sweeps (csrc/sgm_wave.cu) instead of
                                    one kernel per direction.  Moves ~20 instead of ~92 B/pix-disp of
                                    HBM traffic and passes the same parity tests, but is latency-bound
                                    and currently ~5x SLOWER (profiles/r01_v3_fused_sweeps.md).  fp32

@@ -233,10 +233,10 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
   return STM_OK;
 }
 
-// sgm_sweep.cu
-size_t sgm_sweep_workspace_bytes(int H, int W, int D);
-int launch_sgm_sweeps(const float *, const float *, float *, int, int, int, float, float, unsigned,
-                      void *, size_t, cudaStream_t);
+// sgm_wave.cu
+size_t sgm_wave_workspace_bytes(int H, int W, int D);
+int launch_sgm_wave(const float *, const float *, float *, int, int, int, float, float, unsigned,
+                    void *, size_t, cudaStream_t);
 
 static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
   const LaneMap m = pick_lane_map(D);
@@ -245,7 +245,7 @@ static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
 }
 
 size_t sgm_workspace_bytes(int H, int W, int D) {
-  const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_sweep_workspace_bytes(H, W, D);
+  const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_wave_workspace_bytes(H, W, D);
   return a > b ? a : b;
 }
 
@@ -259,9 +259,9 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
     return fail(STM_EINVAL, "sgm: workspace too small (%zu < %zu)", workspace_bytes,
                 sgm_workspace_bytes(H, W, D));
   if (flags & STM_SGM_FUSED_SWEEPS) {
-    // opt-in: two fused raster sweeps (sgm_sweep.cu); 1 = shape not handled there
-    const int rc = launch_sgm_sweeps(cost, image, out, H, W, D, p1, p2, flags, workspace,
-                                     workspace_bytes, stream);
+    // opt-in: two fused raster sweeps (sgm_wave.cu); 1 = shape not handled there
+    const int rc = launch_sgm_wave(cost, image, out, H, W, D, p1, p2, flags, workspace,
+                                   workspace_bytes, stream);
     if (rc != 1) return rc;
   }
   const LaneMap m = pick_lane_map(D);

@@ -41,7 +41,7 @@ def test_workspace_query_is_pure():
     lib.stm_sgm_workspace_bytes.restype = ctypes.c_size_t
 
     def expect(H, W, dpad):
-        # csrc/sgm_sweep.cu: [l-store dir 5][l-store dir 7][CTA->CTA rings: ceil(H/4) x 32 slots
+        # csrc/sgm_wave.cu: [l-store dir 5][l-store dir 7][CTA->CTA rings: ceil(H/4) x 32 slots
         # x 3 vectors][flags: 2 sweeps x {gprog, gcons} x ceil(H/4)], each 16-byte aligned
         a16 = lambda n: (n + 15) // 16 * 16
         g = (H + 3) // 4
