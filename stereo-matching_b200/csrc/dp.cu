@@ -8,9 +8,9 @@
 // Default mode = the reference CUDA functor (ExpandPathsKernelCUDA, :83-130) with its
 // shared-memory race resolved as read-before-write: all three neighbours come from the
 // previous column.  One warp per image row, the D running costs spread over the lanes
-// (lanevec.cuh), neighbours by shuffle, back-pointers stored as packed bytes; forward
-// pass, argmin and backtrack are fused in one kernel so the row's path bytes are re-read
-// while still L2-resident.
+// (lanevec.cuh), neighbours by shuffle, back-pointers stored as packed bytes, the next 8
+// cost vectors prefetched in registers; forward pass, argmin and backtrack are fused in one
+// kernel; the backtrack fetches a +-15 disparity window for 16 columns at a time.
 //
 // STM_DP_CPU_EXACT = the reference CPU functor (ExpandPathsKernelCPU, :24-68) literally,
 // including its transposed column-0 read, its in-place (Gauss-Seidel) scan over d and the
@@ -29,9 +29,10 @@ dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
   if (row >= H) return;
   const size_t row_off = (size_t)row * W;
   const LaneCtx cx = lv_ctx<NV, VW>(lane, D);
+  const float *crow = cost + row_off * D;
 
-  LaneVec<NV, VW> acc, c_next;
-  lv_load<NV, VW, true>(acc, cost + row_off * D, lane, D);
+  LaneVec<NV, VW> acc;
+  lv_load<NV, VW, true>(acc, crow, lane, D);
   // column 0 of the path volume: zero (never read by the backtrack)
   {
     int8_t *p0 = path + row_off * D;
@@ -43,11 +44,17 @@ dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
         if (d < D) p0[d] = 0;
       }
   }
-  if (W > 1) lv_load<NV, VW, true>(c_next, cost + (row_off + 1) * D, lane, D);
 
-  for (int col = 1; col < W; ++col) {
-    LaneVec<NV, VW> cur = c_next;
-    if (col + 1 < W) lv_load<NV, VW, true>(c_next, cost + (row_off + col + 1) * D, lane, D);
+  // ---- forward pass.  The cost vectors of the next PF columns stay in flight in registers;
+  // every load is unconditional (clamped to the row): a load under a branch is waited for at
+  // the join and the pass then runs at one DRAM round trip per column (it did: 1.75 ms).
+  constexpr int PF = (NV * VW <= 4) ? 8 : 4;
+  LaneVec<NV, VW> cbuf[PF];
+#pragma unroll
+  for (int u = 0; u < PF; ++u)
+    lv_load<NV, VW, true>(cbuf[u], crow + (size_t)(1 + u < W ? 1 + u : W - 1) * D, lane, D);
+
+  auto step = [&](const int col, const LaneVec<NV, VW> &cur) {
     LaneVec<NV, VW> lo, hi;
     lv_neighbours<NV, VW>(acc, lo, hi, cx);
     int8_t *pp = path + (row_off + col) * D;
@@ -74,6 +81,24 @@ dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
         if (d0 < D) pp[d0] = dirs[0];
       }
     }
+  };
+
+  int col = 1;
+  for (int g = (W - 1) / PF; g > 0; --g) {
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+      const LaneVec<NV, VW> cur = cbuf[u];
+      lv_load<NV, VW, true>(cbuf[u], crow + (size_t)(col + PF < W ? col + PF : W - 1) * D, lane, D);
+      step(col, cur);
+      ++col;
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < PF; ++u) {
+    if (col < W) {  // tail: already in cbuf, no loads here
+      step(col, cbuf[u]);
+      ++col;
+    }
   }
 
   lv_store<NV, VW, false>(acc, row_final + (size_t)row * D, lane, D);
@@ -97,18 +122,39 @@ dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
   }
   int e = idx == 0x7fffffff ? 0 : idx;
 
-  // backtrack (one lane; the row's path bytes were just written by this warp)
+  // ---- backtrack (reference ReducePathsKernel, src/dynamic_programming.cu:166-181):
+  //   e(col) = clamp(e(col+1) + path[row][col][e(col+1)], 0, D-1).
+  // Literally that is W dependent one-byte loads.  The disparity moves by at most one per
+  // column, so the bytes the next 16 columns can ask for lie within e +- 15: lane l fetches
+  // path[col][e - 16 + l] for 16 columns at once (16 independent loads in flight), then the 16
+  // steps are resolved with shuffles.  The row's path bytes were written by this warp.
   __syncwarp();
-  if (lane == 0) {
-    int32_t *drow = disp + row_off;
-    drow[W - 1] = e;
-    const int8_t *prow = path + row_off * D;
-    for (int col = W - 2; col >= 0; --col) {
-      const int step = __ldcg(reinterpret_cast<const signed char *>(prow + (size_t)col * D + e));
-      e += step;
-      e = e < 0 ? 0 : (e > D - 1 ? D - 1 : e);
-      drow[col] = e;
+  int32_t *drow = disp + row_off;
+  const signed char *prow = reinterpret_cast<const signed char *>(path + row_off * D);
+  if (lane == 0) drow[W - 1] = e;
+  int col_hi = W - 1;  // column whose disparity `e` is known
+  while (col_hi > 0) {
+    const int nb = col_hi < 16 ? col_hi : 16;  // columns col_hi-1 .. col_hi-nb
+    int dl = e - 16 + lane;
+    dl = dl < 0 ? 0 : (dl > D - 1 ? D - 1 : dl);
+    int w[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int c = col_hi - 1 - j;
+      w[j] = __ldcg(prow + (size_t)(c < 0 ? 0 : c) * D + dl);
     }
+    const int e0 = e;
+    int mine = 0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int v = __shfl_sync(FULL, w[j], e - e0 + 16);
+      int en = e + v;
+      en = en < 0 ? 0 : (en > D - 1 ? D - 1 : en);
+      if (j < nb) e = en;
+      if (lane == j) mine = e;
+    }
+    if (lane < nb) drow[col_hi - 1 - lane] = mine;
+    col_hi -= nb;
   }
 }
 

@@ -209,7 +209,14 @@ def test_dp_cpu_exact_golden(sm, golden, case):
 
 @pytest.mark.parametrize("H,W,D,kind", [(20, 50, 32, "ssd"), (9, 33, 64, "ssd"), (12, 40, 128, "ssd"),
                                           (7, 30, 192, "ssd"), (15, 21, 12, "ties"), (6, 1, 32, "ties"),
-                                          (5, 64, 96, "rand")])
+                                          (5, 64, 96, "rand"),
+                                          # forward prefetch groups of 8: none / exactly one / tail
+                                          (4, 2, 32, "rand"), (4, 8, 32, "rand"), (4, 9, 128, "rand"),
+                                          # backtrack windows of 16 columns: edges, many windows
+                                          (3, 16, 64, "rand"), (3, 17, 64, "rand"), (3, 18, 64, "rand"),
+                                          (6, 700, 128, "rand"), (5, 333, 192, "rand"),
+                                          (4, 90, 5, "rand"),    # D smaller than the window
+                                          (3, 120, 256, "rand"), (4, 400, 32, "ties")])
 def test_dp_cuda_mode_vs_oracle(sm, H, W, D, kind):
     if kind == "ssd":
         left, right, _ = synth.random_dot_pair(H, W, D, seed=H + D, scale="raw")
