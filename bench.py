@@ -228,7 +228,7 @@ def run_b200_arm(args):
         time.sleep(0.3)
     launches0 = C.launch_count()
     ms, t0, t1 = timed(step_resident, args.steps)
-    launches = C.launch_count() - launches0
+    launches = int(sharding.sum_over_ranks(C.launch_count() - launches0, dev))  # whole job
     clocks = sampler.stop(t0, t1) if rank == 0 else None
 
     for _ in range(max(1, args.warmup // 2)):
