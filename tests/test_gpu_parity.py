@@ -269,6 +269,27 @@ def test_pipeline_host_entry_point(sm):
     assert np.array_equal(got, O.dp(O.ssd(left, right, D, 7), "cuda"))
 
 
+def test_host_frame_streamer_matches_per_frame_estimate(sm):
+    """Overlapped upload / compute / download returns exactly what Pipeline.estimate returns,
+    for more frames than device buffers and when called twice."""
+    H, W, D = 40, 96, 32
+    frames = [synth.random_dot_pair(H, W, D, seed=400 + f, scale="unit")[:2] for f in range(5)]
+    pipe = sm.Pipeline(sm.cost.SSD(D), sm.disparity_reduce.WinnerTakesAll(), sm.aggregation.Semiglobal())
+    want = [pipe.estimate(cuda(l), cuda(r)).cpu().clone() for l, r in frames]
+    pinned = [(torch.from_numpy(l).pin_memory(), torch.from_numpy(r).pin_memory()) for l, r in frames]
+    outs = [torch.full((H, W), -1, dtype=torch.int32).pin_memory() for _ in frames]
+    streamer = sm.streaming.HostFrameStreamer(pipe, "cuda")
+    for _ in range(2):
+        for o in outs:
+            o.fill_(-1)
+        streamer.run(pinned, outs)
+        torch.cuda.current_stream().synchronize()
+        for got, w in zip(outs, want):
+            assert torch.equal(got, w)
+    with pytest.raises(RuntimeError, match="host tensors"):
+        streamer.run([(cuda(frames[0][0]), cuda(frames[0][1]))], outs[:1])
+
+
 def test_errors_mirror_the_reference(sm):
     img = torch.zeros(8, 8, device="cuda")
     with pytest.raises(RuntimeError, match="type not supported"):
