@@ -82,6 +82,17 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
                 float penalty1, float penalty2, unsigned flags, void *workspace,
                 size_t workspace_bytes, void *stream);
 
+/* Aggregation and winner-takes-all in one call (what Pipeline.estimate does for
+ * Semiglobal + WinnerTakesAll, reference stereomatch/pipeline.py:85-92): same result as
+ * stm_sgm_f32 followed by stm_wta_f32 on `out`, but the argmin is taken inside the last
+ * aggregation pass, so the aggregated volume is never re-read.  To let that pass visit every
+ * pixel exactly once, the last two directions are run in swapped order (6 after 7): `out`
+ * equals stm_sgm_f32's result up to fp32 association (a few ulp).  `out` is still written.
+ * flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE. */
+int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *disparity, int H,
+                    int W, int D, float penalty1, float penalty2, unsigned flags, void *workspace,
+                    size_t workspace_bytes, void *stream);
+
 /* Replaces DisparityReduceOps.run_winners_take_all(cost, disparity)
  * (reference src/disparity_reduce.cpp:6-9 -> RunWinnersTakeAll, src/winners_take_all.cu:89-114).
  * CPU rule: first (lowest-d) minimum, all-inf -> 0, NaN never wins.  Any D >= 1. */

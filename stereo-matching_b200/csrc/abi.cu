@@ -18,7 +18,7 @@ int launch_ssd(const float *, const float *, float *, int, int, int, int, cudaSt
 int launch_birchfield(const float *, const float *, float *, int, int, int, cudaStream_t);
 size_t sgm_workspace_bytes(int, int, int);
 int launch_sgm(const float *, const float *, float *, int, int, int, float, float, unsigned, void *,
-               size_t, cudaStream_t);
+               size_t, cudaStream_t, int32_t *disp = nullptr);
 int launch_dp(const float *, int8_t *, float *, int32_t *, int, int, int, unsigned, cudaStream_t);
 
 static int require_device() {
@@ -108,6 +108,20 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
                     workspace_bytes, (cudaStream_t)stream);
 }
 
+int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *disparity, int H,
+                    int W, int D, float penalty1, float penalty2, unsigned flags, void *workspace,
+                    size_t workspace_bytes, void *stream) {
+  int rc = check_shape("sgm_wta", H, W, D);
+  if (rc) return rc;
+  STM_REQUIRE(cost && left && out && disparity, "sgm_wta: null pointer");
+  STM_REQUIRE(cost != out, "sgm_wta: output must not alias the cost volume");
+  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE)) == 0, "sgm_wta: unknown flags 0x%x",
+              flags);
+  if ((rc = require_device())) return rc;
+  return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace, workspace_bytes,
+                    (cudaStream_t)stream, disparity);
+}
+
 int stm_wta_f32(const float *cost, int32_t *disparity, int H, int W, int D, void *stream) {
   int rc = check_shape("wta", H, W, D);
   if (rc) return rc;
@@ -159,12 +173,16 @@ int stm_pipeline_host_f32(const float *left, const float *right, int32_t *dispar
   if (use_sgm) {
     const size_t wsb = sgm_workspace_bytes(H, W, D);
     if ((rc = s.ensure(kS, N * 4)) || (rc = s.ensure(kWs, wsb ? wsb : 16))) return rc;
+    const bool fuse_wta = reducer == 0 && !(sgm_flags & STM_SGM_FUSED_SWEEPS);
     rc = launch_sgm(dc, dl, (float *)s.ptr[kS], H, W, D, penalty1, penalty2,
-                    sgm_flags | STM_SGM_OVERWRITE, s.ptr[kWs], s.cap[kWs], st);
+                    sgm_flags | STM_SGM_OVERWRITE, s.ptr[kWs], s.cap[kWs], st,
+                    fuse_wta ? (int32_t *)s.ptr[kDisp] : nullptr);
     if (rc) return rc;
     vol = (float *)s.ptr[kS];
+    if (fuse_wta) reducer = -1;  // the last aggregation pass already wrote the disparity map
   }
-  if (reducer == 0) {
+  if (reducer < 0) {
+  } else if (reducer == 0) {
     rc = launch_wta(vol, (int32_t *)s.ptr[kDisp], H, W, D, st);
   } else {
     if ((rc = s.ensure(kPath, N)) || (rc = s.ensure(kRowFinal, (size_t)H * D * 4))) return rc;

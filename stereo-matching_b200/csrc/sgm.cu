@@ -21,14 +21,44 @@
 
 namespace stm {
 
-enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u };
+enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u, kSgmEmitWta = 8u };
 
-template <int NV, int VW, bool ACC>
+// Winner-takes-all of one pixel's vector held across the warp, with the rule of wta.cu /
+// reference src/winners_take_all.cu:21-40: first (lowest-d) minimum, all-inf -> 0, NaN never
+// wins, NaN at d = 0 -> 0.  Used when the LAST aggregation pass also emits the disparity map.
+template <int NV, int VW>
+__device__ __forceinline__ void lv_argmin_store(const LaneVec<NV, VW> &o, int lane, int D,
+                                                int32_t *dst) {
+  // two warp reductions instead of a (value, index) shuffle butterfly, which costs this
+  // latency-sensitive kernel as much as the separate WTA pass it replaces (measured):
+  // m = minimum over the non-NaN entries (redux.sync.min.f32 returns the non-NaN operand),
+  // then the lowest d whose entry equals m (integer redux).  All-inf: m = inf matches d = 0.
+  float m = CUDART_INF_F;
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int j = 0; j < VW; ++j)
+      if (lv_d<NV, VW>(lane, k, j) < D) m = fminf(m, o.v[k][j]);
+  m = warp_min_f32(m);
+  unsigned idx = 0x7fffffffu;
+#pragma unroll
+  for (int k = NV - 1; k >= 0; --k)
+#pragma unroll
+    for (int j = VW - 1; j >= 0; --j) {
+      const int d = lv_d<NV, VW>(lane, k, j);
+      if (d < D && o.v[k][j] == m) idx = (unsigned)d;  // descending d: the lowest one sticks
+    }
+  idx = __reduce_min_sync(FULL, idx);
+  const bool nan0 = __shfl_sync(FULL, (o.v[0][0] != o.v[0][0]) ? 1 : 0, 0) != 0;
+  if (lane == 0) *dst = (nan0 || idx == 0x7fffffffu) ? 0 : (int)idx;
+}
+
+template <int NV, int VW, bool ACC, bool WTA>
 __global__ void __launch_bounds__(128)
 sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
                 float *__restrict__ out, int H, int W, int D, float p1, float p2, int dir,
                 int path_begin, int path_count, int min_limit, unsigned mode,
-                float *__restrict__ l_store, int l_store_path) {
+                float *__restrict__ l_store, int l_store_path, int32_t *__restrict__ disp) {
   const int lane = threadIdx.x & 31;
   const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (w >= path_count) return;
@@ -73,6 +103,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
 #pragma unroll
         for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
       lv_store<NV, VW, true>(o, optr, 0, dl);
+      if (WTA) lv_argmin_store<NV, VW>(o, lane, D, disp + pix0);
     } else {
       lv_store<NV, VW, true>(L, optr, 0, dl);
     }
@@ -117,6 +148,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
 #pragma unroll
             for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
           lv_store<NV, VW, true>(o, optr, 0, dl);
+          if (WTA) lv_argmin_store<NV, VW>(o, lane, D, disp + pix0 + (long long)(i + u) * step);
         } else {
           lv_store<NV, VW, true>(L, optr, 0, dl);
         }
@@ -145,17 +177,21 @@ template <int NV, int VW>
 static int run_direction(const float *cost, const float *image, float *out, int H, int W, int D,
                          float p1, float p2, int dir, int path_begin, int path_count,
                          int min_limit, unsigned mode, float *l_store, int l_store_path,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, int32_t *disp = nullptr) {
   const int warps = 4;
   const int blocks = (path_count + warps - 1) / warps;
-  if (mode & kSgmAccumulate)
-    sgm_path_kernel<NV, VW, true><<<blocks, warps * 32, 0, stream>>>(
+  if ((mode & kSgmEmitWta) && disp)  // last pass of the fused aggregate+reduce call
+    sgm_path_kernel<NV, VW, true, true><<<blocks, warps * 32, 0, stream>>>(
         cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
-        l_store_path);
+        l_store_path, disp);
+  else if (mode & kSgmAccumulate)
+    sgm_path_kernel<NV, VW, true, false><<<blocks, warps * 32, 0, stream>>>(
+        cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
+        l_store_path, nullptr);
   else
-    sgm_path_kernel<NV, VW, false><<<blocks, warps * 32, 0, stream>>>(
+    sgm_path_kernel<NV, VW, false, false><<<blocks, warps * 32, 0, stream>>>(
         cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
-        l_store_path);
+        l_store_path, nullptr);
   return check_launch("sgm_path_kernel");
 }
 
@@ -171,17 +207,25 @@ int sgm_repeat_add(float *out, float *l_store, int H, int W, int D, int dpad, in
 template <int NV, int VW>
 static int sgm_by_direction(const float *cost, const float *image, float *out, int H, int W,
                             int D, float p1, float p2, unsigned flags, float *ws,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, int32_t *disp) {
   const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
   const int dpad = NV * 32 * VW;
   int rc;
-  for (int dir = 0; dir < 8; ++dir) {
+  // Reference order 0..7.  When the disparity map is emitted by the last pass, that pass must
+  // visit every pixel exactly once after everything else (the corner-diagonal replays
+  // included); direction 7 skips a band of pixels on landscape images, so the
+  // last two directions swap and direction 6 runs last.
+  const int plain[8] = {0, 1, 2, 3, 4, 5, 6, 7}, fused[8] = {0, 1, 2, 3, 4, 5, 7, 6};
+  const int *order = disp ? fused : plain;
+  for (int pass = 0; pass < 8; ++pass) {
+    const int dir = order[pass];
     const int np = sgm_num_paths(dir, H, W);
-    unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
+    unsigned mode = (pass == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
+    if (disp && pass == 7) mode |= kSgmEmitWta;
     const int multi = sgm_multi_path_index(dir, H, W);
     if (multi < 0) {
       rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, 0, np, min_limit, mode,
-                                 nullptr, -1, stream);
+                                 nullptr, -1, stream, disp);
       if (rc) return rc;
       continue;
     }
@@ -208,13 +252,14 @@ static int sgm_by_direction(const float *cost, const float *image, float *out, i
 template <int NV, int VW>
 static int sgm_by_direction_portrait(const float *cost, const float *image, float *out, int H,
                                      int W, int D, float p1, float p2, unsigned flags, float *ws,
-                                     cudaStream_t stream) {
+                                     cudaStream_t stream, int32_t *disp) {
   const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
   const int dpad = NV * 32 * VW;
   int rc;
   for (int dir = 0; dir < 8; ++dir) {
     const int np = sgm_num_paths(dir, H, W);
-    const unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
+    unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
+    if (disp && dir == 7) mode |= kSgmEmitWta;  // portrait: direction 7 visits every pixel once
     if (dir == 4) {
       const int multi = sgm_multi_path_index(5, H, W);
       const int times = sgm_path_geom(5, multi, H, W).mult - 1;
@@ -227,7 +272,7 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
       }
     }
     rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, 0, np, min_limit, mode,
-                               nullptr, -1, stream);
+                               nullptr, -1, stream, disp);
     if (rc) return rc;
   }
   return STM_OK;
@@ -251,14 +296,14 @@ size_t sgm_workspace_bytes(int H, int W, int D) {
 
 int launch_sgm(const float *cost, const float *image, float *out, int H, int W, int D, float p1,
                float p2, unsigned flags, void *workspace, size_t workspace_bytes,
-               cudaStream_t stream) {
+               cudaStream_t stream, int32_t *disp) {
   if (D < 2) return fail(STM_EINVAL, "sgm: D must be >= 2");
   if (H > 32767 || W > 32767)  // the reference stores coordinates as int16 (semiglobal.hpp:34-36)
     return fail(STM_EINVAL, "sgm: H and W must be <= 32767");
   if (workspace_bytes < sgm_workspace_bytes(H, W, D) || (workspace == nullptr && H != W))
     return fail(STM_EINVAL, "sgm: workspace too small (%zu < %zu)", workspace_bytes,
                 sgm_workspace_bytes(H, W, D));
-  if (flags & STM_SGM_FUSED_SWEEPS) {
+  if ((flags & STM_SGM_FUSED_SWEEPS) && !disp) {
     // opt-in: two fused raster sweeps (sgm_wave.cu); 1 = shape not handled there
     const int rc = launch_sgm_wave(cost, image, out, H, W, D, p1, p2, flags, workspace,
                                    workspace_bytes, stream);
@@ -269,9 +314,9 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
 #define STM_SGM_CASE(NV_, VW_)                                                            \
   if (m.NV == NV_ && m.VW == VW_)                                                         \
     return H > W ? sgm_by_direction_portrait<NV_, VW_>(cost, image, out, H, W, D, p1, p2,  \
-                                                       flags, ws, stream)                 \
+                                                       flags, ws, stream, disp)           \
                  : sgm_by_direction<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags,    \
-                                              ws, stream);
+                                              ws, stream, disp);
   STM_SGM_CASE(1, 4) STM_SGM_CASE(2, 4) STM_SGM_CASE(3, 4) STM_SGM_CASE(4, 4)
   STM_SGM_CASE(1, 2) STM_SGM_CASE(3, 2) STM_SGM_CASE(5, 2) STM_SGM_CASE(7, 2)
   STM_SGM_CASE(1, 1) STM_SGM_CASE(2, 1) STM_SGM_CASE(3, 1) STM_SGM_CASE(4, 1)

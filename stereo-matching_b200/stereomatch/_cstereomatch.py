@@ -40,10 +40,11 @@ _lib.stm_sgm_workspace_bytes.argtypes = [_i, _i, _i]
 _lib.stm_sgm_workspace_bytes.restype = _sz
 _lib.stm_sgm_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _f, _f, _u, _vp, _sz, _vp]
 _lib.stm_wta_f32.argtypes = [_vp, _vp, _i, _i, _i, _vp]
+_lib.stm_sgm_wta_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _u, _vp, _sz, _vp]
 _lib.stm_dp_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _u, _vp]
 _lib.stm_pipeline_host_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _u, _i, _u]
-for _name in ("stm_ssd_f32", "stm_birchfield_f32", "stm_sgm_f32", "stm_wta_f32", "stm_dp_f32",
-              "stm_pipeline_host_f32"):
+for _name in ("stm_ssd_f32", "stm_birchfield_f32", "stm_sgm_f32", "stm_sgm_wta_f32", "stm_wta_f32",
+              "stm_dp_f32", "stm_pipeline_host_f32"):
     getattr(_lib, _name).restype = _i
 
 
@@ -150,6 +151,29 @@ class AggregationOps:
             _check(_lib.stm_sgm_f32(cost.data_ptr(), left.data_ptr(), out.data_ptr(), H, W, D,
                                     float(penalty1), float(penalty2), int(flags), ws.data_ptr(),
                                     ws.numel(), _stream()))
+
+
+    @staticmethod
+    def run_semiglobal_wta(cost_volume, left_image, penalty1: float, penalty2: float,
+                           output_cost_volume, disparity_image, flags: int = 0) -> None:
+        """New: run_semiglobal + run_winners_take_all in one call (include/stm_abi.h,
+        stm_sgm_wta_f32); the argmin is taken inside the last aggregation pass."""
+        cost = _gpu("RunSemiglobal: cost_volume", cost_volume, torch.float32, 3)
+        left = _gpu("RunSemiglobal: left_image", left_image, torch.float32, 2, cost)
+        out = _out("output_cost_volume",
+                   _gpu("RunSemiglobal: output_cost_volume", output_cost_volume, torch.float32, 3, cost))
+        disp = _out("disparity_image",
+                    _gpu("RunWinnersTakeAll: disparity_image", disparity_image, torch.int32, 2, cost))
+        if out.shape != cost.shape or tuple(left.shape) != tuple(cost.shape[:2]) or \
+                tuple(disp.shape) != tuple(cost.shape[:2]):
+            raise RuntimeError("RunSemiglobal: shapes do not match")
+        cost, left = cost.contiguous(), left.contiguous()
+        H, W, D = cost.shape
+        ws = _sgm_workspace(cost.device, int(_lib.stm_sgm_workspace_bytes(H, W, D)))
+        with torch.cuda.device(cost.device):
+            _check(_lib.stm_sgm_wta_f32(cost.data_ptr(), left.data_ptr(), out.data_ptr(),
+                                        disp.data_ptr(), H, W, D, float(penalty1), float(penalty2),
+                                        int(flags), ws.data_ptr(), ws.numel(), _stream()))
 
 
 class DisparityReduceOps:

@@ -43,3 +43,20 @@ class Semiglobal:
         _AggregationOps.run_semiglobal(cost_volume, left_image, self.penalty1, self.penalty2,
                                        sga_volume, flags)
         return sga_volume
+
+    def aggregate_and_reduce(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
+                             sga_volume: Optional[torch.Tensor] = None,
+                             disparity_img: Optional[torch.Tensor] = None):
+        """New: aggregation followed by winner-takes-all in one native call; returns
+        (sga_volume, disparity_img).  The argmin is taken inside the last aggregation pass, so
+        the aggregated volume is not re-read; that pass must visit every pixel once, hence the
+        last two directions run in swapped order and sga_volume equals __call__'s result up to
+        fp32 association.  The disparity map is exactly WinnerTakesAll()(sga_volume)."""
+        sga_volume = empty_tensor(*cost_volume.size(), dtype=cost_volume.dtype,
+                                  device=cost_volume.device, reuse_tensor=sga_volume)
+        disparity_img = empty_tensor(cost_volume.size(0), cost_volume.size(1), dtype=torch.int32,
+                                     device=cost_volume.device, reuse_tensor=disparity_img)
+        flags = STM_SGM_OVERWRITE | (STM_SGM_MIN_ALL_D if self.min_over_all_d else 0)
+        _AggregationOps.run_semiglobal_wta(cost_volume, left_image, self.penalty1, self.penalty2,
+                                           sga_volume, disparity_img, flags)
+        return sga_volume, disparity_img

@@ -3,6 +3,9 @@ from typing import Callable, Optional
 
 import torch
 
+from .aggregation import Semiglobal
+from .disparity_reduce import WinnerTakesAll
+
 CostFunction = Callable[[torch.Tensor, torch.Tensor, torch.Tensor], torch.Tensor]
 AggregationFunction = Callable[[torch.Tensor, torch.Tensor, torch.Tensor], torch.Tensor]
 DisparityReduceFunction = Callable[[torch.Tensor, torch.Tensor], torch.Tensor]
@@ -20,6 +23,9 @@ class Pipeline:
         self._cost_volume = None
         self._aggregation_volume = None
         self._disparity_image = None
+        # New: Semiglobal followed by WinnerTakesAll runs as one native call (the argmin is
+        # folded into the last aggregation pass).  Set to False for two separate stages.
+        self.fuse_aggregation_and_reduce = True
 
     def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor) -> torch.Tensor:
         """[H,W] left/right images (CUDA float32) -> int32 [H,W] disparity map."""
@@ -28,6 +34,12 @@ class Pipeline:
             own = self._aggregation_volume
             if own is self._cost_volume:  # left over from a run without aggregation
                 own = None
+            if (self.fuse_aggregation_and_reduce and type(self.disparity_reduce) is WinnerTakesAll
+                    and type(self.aggregation) is Semiglobal and not self.aggregation.fused_sweeps):
+                self._aggregation_volume, self._disparity_image = self.aggregation.aggregate_and_reduce(
+                    self._cost_volume, left_image.to(self._cost_volume.device), own,
+                    self._disparity_image)
+                return self._disparity_image
             self._aggregation_volume = self.aggregation(
                 self._cost_volume, left_image.to(self._cost_volume.device), own)
         else:

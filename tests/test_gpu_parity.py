@@ -269,6 +269,59 @@ def test_pipeline_host_entry_point(sm):
     assert np.array_equal(got, O.dp(O.ssd(left, right, D, 7), "cuda"))
 
 
+@pytest.mark.parametrize("H,W,D,kind", [(26, 41, 32, "ssd"), (41, 26, 32, "ssd"), (20, 20, 64, "ssd"),
+                                          (17, 60, 128, "ssd"), (13, 35, 192, "ssd"), (11, 29, 20, "ssd"),
+                                          (9, 33, 32, "ties"), (1, 9, 32, "ssd"), (9, 1, 32, "ssd"),
+                                          (70, 150, 128, "ssd")])
+def test_sgm_with_wta_folded_into_the_last_pass(sm, H, W, D, kind):
+    """stm_sgm_wta_f32: the disparity map is EXACTLY WinnerTakesAll of the volume it returns
+    (landscape, portrait, square, ties, odd D), and that volume is the oracle's SGM to 1e-4."""
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 5 + W, scale="unit")
+    cost = O.ssd(left, right, D, 3) if kind == "ssd" else synth.tie_heavy_volume(H, W, D, seed=D)
+    c, l = cuda(cost), cuda(left)
+    sgm = sm.aggregation.Semiglobal()
+    vol, disp = sgm.aggregate_and_reduce(c, l)
+    assert disp.dtype == torch.int32 and tuple(disp.shape) == (H, W)
+    assert_volume_close(vol, O.sgm(cost, left, 0.1, 0.2))
+    assert np.array_equal(disp.cpu().numpy(), O.wta(vol.cpu().numpy()))
+    assert torch.equal(disp, sm.disparity_reduce.WinnerTakesAll()(vol))
+    # buffers are reused when passed back in
+    vol2, disp2 = sgm.aggregate_and_reduce(c, l, vol, disp)
+    assert vol2.data_ptr() == vol.data_ptr() and disp2.data_ptr() == disp.data_ptr()
+
+
+def test_sgm_wta_fold_argmin_rule_with_nan_and_inf(sm):
+    """Pixels whose whole cost vector is +inf turn into NaN sums (inf - inf) that spread along
+    the paths: the folded argmin must follow the same rule as the WTA kernel and the oracle
+    (first minimum, NaN never wins, NaN at d = 0 -> 0, all-inf -> 0) on the SAME volume."""
+    H, W, D = 12, 20, 32
+    vol = synth.random_volume(H, W, D, seed=5, hi=10.0)
+    vol[3, 4, :] = np.inf
+    vol[7, 11, :] = np.inf
+    vol[5, 6, 0] = np.inf
+    vol[:, 0, 1:] = np.inf          # like d > x
+    img = synth.random_volume(H, W, 1, seed=6, hi=255.0)[:, :, 0]
+    agg, disp = sm.aggregation.Semiglobal().aggregate_and_reduce(cuda(vol), cuda(img))
+    a = agg.cpu().numpy()
+    assert np.isnan(a).any() and np.isinf(a).any()      # the case is what it claims to be
+    assert np.array_equal(disp.cpu().numpy(), O.wta(a))
+    assert torch.equal(disp, sm.disparity_reduce.WinnerTakesAll()(agg))
+
+
+def test_pipeline_fused_and_unfused_agree(sm):
+    H, W, D = 48, 96, 32
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=99, scale="unit")
+    l, r = cuda(left), cuda(right)
+    mk = lambda: sm.Pipeline(sm.cost.SSD(D), sm.disparity_reduce.WinnerTakesAll(), sm.aggregation.Semiglobal())
+    fused, plain = mk(), mk()
+    plain.fuse_aggregation_and_reduce = False
+    a, b = fused.estimate(l, r), plain.estimate(l, r)
+    assert float((a != b).float().mean()) <= 1e-3   # north_star: <= 0.1 % of pixels
+    want = O.wta(O.sgm(O.ssd(left, right, D, 7), left, 0.1, 0.2))
+    assert float((a.cpu().numpy() != want).mean()) <= 1e-3
+    assert float((b.cpu().numpy() != want).mean()) <= 1e-3
+
+
 def test_host_frame_streamer_matches_per_frame_estimate(sm):
     """Overlapped upload / compute / download returns exactly what Pipeline.estimate returns,
     for more frames than device buffers and when called twice."""
