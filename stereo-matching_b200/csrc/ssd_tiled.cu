@@ -67,22 +67,35 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
   const int cbase = x0 - K;            // image column of staged column 0
   const int ubase = cbase - d0 - (DC - 1);  // right-image column of rrow[.][0]
 
-  // cooperative staging of one image row (zeros outside the image)
-  auto stage = [&](int t, int buf) {
-    const int r = ya - K + t;
-    const bool row_ok = (r >= 0) && (r < H);
-    if (tid < TXH) {
-      const int c = cbase + tid;
-      lrow[buf][tid] = (row_ok && c >= 0 && c < W) ? __ldg(left + (size_t)r * W + c) : 0.f;
-    } else if (tid < TXH + Cfg::RROW) {
-      const int i = tid - TXH;
-      const int u = ubase + i;
-      rrow[buf][i] = (row_ok && u >= 0 && u < W) ? __ldg(right + (size_t)r * W + u) : 0.f;
-    }
-  };
+  // Cooperative staging of the image rows (zeros outside the image), software-pipelined through
+  // one register: a row is LOADED two iterations before it is used and STORED to shared memory
+  // one iteration before, so no global-load latency sits between two row barriers.  The load is
+  // unconditional (clamped address, value masked when it is stored): a load under a branch
+  // would be waited for at the join.  Threads [0,TXH) stage the left row, the next RROW the
+  // right row; the other vertical threads load a clamped address and store nothing.
   static_assert(Cfg::VTHREADS >= TXH + Cfg::RROW, "not enough loader threads");
+  const bool st_left = tid < TXH;
+  const bool st_any = tid < TXH + Cfg::RROW;
+  const int st_col = st_left ? cbase + tid : ubase + (tid - TXH);
+  const bool st_col_ok = st_any && st_col >= 0 && st_col < W;
+  const float *st_src = (st_left ? left : right) + min(max(st_col, 0), W - 1);
+  float *st_dst0 = st_left ? &lrow[0][tid] : &rrow[0][st_any ? tid - TXH : 0];
+  const int st_stride = st_left ? TXH : Cfg::RROW + 1;  // floats between the two buffers
+  auto fetch = [&](int t) -> float {  // raw value of staged row t (any t)
+    const int r = min(max(ya - K + t, 0), H - 1);
+    return __ldg(st_src + (size_t)r * W);
+  };
+  auto put = [&](int t, float raw) {  // store staged row t into buffer t&1
+    const int r = ya - K + t;
+    const bool ok = st_col_ok && r >= 0 && r < H;
+    if (st_any) st_dst0[(t & 1) * st_stride] = ok ? raw : 0.f;
+  };
 
-  stage(0, 0);
+  float staged = 0.f;  // raw value of row t+1 while iteration t runs (vertical role only)
+  if (tid < Cfg::VTHREADS) {
+    put(0, fetch(0));
+    staged = fetch(1);
+  }
   __syncthreads();
 
   if (tid < Cfg::VTHREADS) {
@@ -104,37 +117,52 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
 #pragma unroll
       for (int j = 0; j < 4; ++j) ring[i][j] = 0.f;
 
-    for (int tb = 0; tb < T; tb += WIN) {
+    // one input row: jj is a compile-time constant after unrolling (static ring indices)
+    auto row_step = [&](int t, int jj) {
+      const int buf = t & 1;
+      // row t+1 (loaded one iteration ago) goes to shared memory, row t+2 is requested.  Past
+      // the last row both are harmless: the address is clamped and nobody reads the buffer.
+      put(t + 1, staged);
+      staged = fetch(t + 2);
+      float out[4];
+      if (active) {
+        const float l = lrow[buf][cl];
 #pragma unroll
-      for (int jj = 0; jj < WIN; ++jj) {
-        const int t = tb + jj;
-        if (t < T) {  // block-uniform
-          const int buf = t & 1;
-          if (t + 1 < T) stage(t + 1, buf ^ 1);
-          float out[4];
-          if (active) {
-            const float l = lrow[buf][cl];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const float diff = __fsub_rn(l, rrow[buf][rbase - j]);
-              const float e = valid[j] ? __fmul_rn(diff, diff) : 0.f;
-              pre[j] = __fadd_rn(pre[j], e);
-              out[j] = (jj < WIN - 1) ? __fadd_rn(ring[(jj + 1) % WIN][j], pre[j]) : pre[j];
-              ring[jj][j] = e;
-            }
-            *reinterpret_cast<float4 *>(&vbuf[buf][cl][dq * 4]) =
-                make_float4(out[0], out[1], out[2], out[3]);
-          }
-          named_barrier(Cfg::THREADS);
+        for (int j = 0; j < 4; ++j) {
+          const float diff = __fsub_rn(l, rrow[buf][rbase - j]);
+          const float e = valid[j] ? __fmul_rn(diff, diff) : 0.f;
+          pre[j] = __fadd_rn(pre[j], e);
+          out[j] = (jj < WIN - 1) ? __fadd_rn(ring[(jj + 1) % WIN][j], pre[j]) : pre[j];
+          ring[jj][j] = e;
         }
+        *reinterpret_cast<float4 *>(&vbuf[buf][cl][dq * 4]) =
+            make_float4(out[0], out[1], out[2], out[3]);
       }
-      // turn the finished block of raw values into suffix sums; restart the prefix
+      named_barrier(Cfg::THREADS);
+    };
+    // turn the finished block of raw values into suffix sums; restart the prefix
+    auto close_block = [&]() {
 #pragma unroll
       for (int i = WIN - 2; i >= 1; --i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) ring[i][j] = __fadd_rn(ring[i][j], ring[i + 1][j]);
 #pragma unroll
       for (int j = 0; j < 4; ++j) pre[j] = 0.f;
+    };
+
+    // Full blocks run without any `t < T` test: a load whose result is merged at the join of
+    // a branch is waited for at that join, which would put the global latency of `fetch`
+    // back between two barriers.  Only the last, partial block is guarded.
+    int tb = 0;
+    for (; tb + WIN <= T; tb += WIN) {
+#pragma unroll
+      for (int jj = 0; jj < WIN; ++jj) row_step(tb + jj, jj);
+      close_block();
+    }
+    if (tb < T) {
+#pragma unroll
+      for (int jj = 0; jj < WIN; ++jj)
+        if (tb + jj < T) row_step(tb + jj, jj);  // block-uniform
     }
   } else {
     // ----------------------------- horizontal role -----------------------------------
@@ -143,6 +171,7 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
     const int d = d0 + lane;
     const bool d_ok = d < D;
     const int xr = x0 + q * WIN;
+    const bool interior = (xr + WIN <= W) && (xr >= d0 + DC - 1) && (d0 + DC <= D);  // warp-uniform
     auto emit = [&](int t) {
       // row produced by the vertical warps in iteration t
       const int y = ya - WIN + 1 + t;
@@ -157,11 +186,21 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
 #pragma unroll
       for (int i = WIN + 1; i < 2 * WIN - 1; ++i) v[i] = __fadd_rn(v[i], v[i - 1]);
       float *orow = cost + ((size_t)y * W + xr) * D + d;
+      if (interior) {
+        // the whole run lies inside the image, right of every disparity of the chunk, and the
+        // chunk inside [0,D): nothing to test per store (these 4 warps are the serial part of
+        // a row, ~200 instructions each with the tests, ~110 without)
+        asm volatile("" : "+l"(orow));  // opaque base: keeps the index arithmetic out of the loop
 #pragma unroll
-      for (int j = 0; j < WIN; ++j) {
-        const int x = xr + j;
-        const float s = (j == 0) ? v[0] : __fadd_rn(v[j], v[WIN + j - 1]);
-        if (d_ok && x < W) __stcs(orow + (size_t)j * D, d > x ? CUDART_INF_F : s);
+        for (int j = 0; j < WIN; ++j)  // 32-bit offsets: one IMAD.WIDE per address
+          __stcs(orow + j * D, (j == 0) ? v[0] : __fadd_rn(v[j], v[WIN + j - 1]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < WIN; ++j) {
+          const int x = xr + j;
+          const float s = (j == 0) ? v[0] : __fadd_rn(v[j], v[WIN + j - 1]);
+          if (d_ok && x < W) __stcs(orow + (size_t)j * D, d > x ? CUDART_INF_F : s);
+        }
       }
     };
     for (int t = 0; t < T; ++t) {

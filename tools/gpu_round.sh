@@ -18,6 +18,9 @@ if [ $PYTEST_RC -ne 0 ]; then
   exit $PYTEST_RC
 fi
 
+echo "== smoke()"
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/${TAG}_smoke.log 2>&1; echo "smoke exit=$?"; tail -1 $OUT/${TAG}_smoke.log
+
 echo "== stage bench"
 timeout 300 python tools/stage_bench.py 1080 1920 128 > $OUT/${TAG}_stages_1080p_d128.json 2> $OUT/${TAG}_stages.err
 echo "stage_bench exit=$?"; cat $OUT/${TAG}_stages_1080p_d128.json
