@@ -48,6 +48,10 @@ extern "C" {
                                    HBM traffic and passes the same parity tests, but is latency-bound
                                    and currently ~5x SLOWER (profiles/r01_v3_fused_sweeps.md).  fp32
                                    sums associate differently (same values within a few ulp). */
+#define STM_SGM_DISPARITY_ONLY 8u /* stm_sgm_wta_f32 only: `out` is scratch.  The last pass reduces
+                                     the finished sums to the disparity map without writing them
+                                     back (4 B/pix-disp less HBM traffic); on return `out` holds
+                                     the sum of the first seven directions, not the result. */
 
 /* flags of stm_dp_f32 */
 #define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68);
@@ -87,8 +91,10 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
  * stm_sgm_f32 followed by stm_wta_f32 on `out`, but the argmin is taken inside the last
  * aggregation pass, so the aggregated volume is never re-read.  To let that pass visit every
  * pixel exactly once, the last two directions are run in swapped order (6 after 7): `out`
- * equals stm_sgm_f32's result up to fp32 association (a few ulp).  `out` is still written.
- * flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE. */
+ * equals stm_sgm_f32's result up to fp32 association (a few ulp).  `out` is still written
+ * unless STM_SGM_DISPARITY_ONLY is given (what Pipeline.estimate uses: it never hands the
+ * aggregated volume to its caller).
+ * flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY. */
 int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *disparity, int H,
                     int W, int D, float penalty1, float penalty2, unsigned flags, void *workspace,
                     size_t workspace_bytes, void *stream);

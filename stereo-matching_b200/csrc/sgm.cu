@@ -21,7 +21,8 @@
 
 namespace stm {
 
-enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u, kSgmEmitWta = 8u };
+enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u, kSgmEmitWta = 8u,
+                  kSgmSkipVolumeStore = 16u /* with kSgmEmitWta: the sum is reduced, not written */ };
 
 // Winner-takes-all of one pixel's vector held across the warp, with the rule of wta.cu /
 // reference src/winners_take_all.cu:21-40: first (lowest-d) minimum, all-inf -> 0, NaN never
@@ -53,8 +54,25 @@ __device__ __forceinline__ void lv_argmin_store(const LaneVec<NV, VW> &o, int la
   if (lane == 0) *dst = (nan0 || idx == 0x7fffffffu) ? 0 : (int)idx;
 }
 
-template <int NV, int VW, bool ACC, bool WTA>
-__global__ void __launch_bounds__(128)
+// Prefetch depth per lane-vector size.  PFSEL 0 = default; 1 = deep (twice as many pixels in
+// flight, for directions with so few paths that they all fit on the GPU anyway); 2 = shallow:
+// at most 128 registers, so 4 instead of 3 CTAs (16 instead of 12 warps) are resident per SM
+// and all 1920 vertical paths of a 1080p frame run in ONE wave instead of 1776 + a 144-warp
+// tail that costs a full chain of 1080 dependent steps at next to no bandwidth.  (CTAs stay
+// at 4 warps: registers are allocated per 4 warps, a 2-warp CTA pays for 4.)
+template <int NV, int VW, int PFSEL>
+struct SgmPf {
+  static constexpr int kBase = (NV * VW <= 4) ? 8 : ((NV * VW <= 6) ? 5 : 4);
+  static constexpr bool kHasDeep = NV * VW <= 4;     // larger vectors would spill at twice the depth
+  static constexpr bool kHasShallow = NV * VW <= 4;  // larger vectors cannot get under 128 registers
+  static constexpr int value = (PFSEL == 1 && kHasDeep) ? 2 * kBase
+                               : ((PFSEL == 2 && kHasShallow) ? 5 : kBase);
+  static constexpr int kThreads = 128;
+  static constexpr int kMinBlocks = (PFSEL == 2 && kHasShallow) ? 4 : 0;  // 0 = unspecified
+};
+
+template <int NV, int VW, bool ACC, bool WTA, int PFSEL>
+__global__ void __launch_bounds__(SgmPf<NV, VW, PFSEL>::kThreads, SgmPf<NV, VW, PFSEL>::kMinBlocks)
 sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
                 float *__restrict__ out, int H, int W, int D, float p1, float p2, int dir,
                 int path_begin, int path_count, int min_limit, unsigned mode,
@@ -67,6 +85,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
   if (g.mult == 0) return;
   const bool write_out = !(mode & kSgmNoOutput);
   const bool store_l = (mode & kSgmStoreL) && path == l_store_path;
+  const bool store_vol = !(WTA && (mode & kSgmSkipVolumeStore));
   constexpr int dpad = NV * 32 * VW;
 
   // Pixel i of the path sits at pix0 + i*step: addresses are known up front, so the cost
@@ -74,7 +93,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
   // PF pixels are kept in flight in registers while the recurrence runs.  The loop runs
   // whole groups of PF pixels: prefetches past the end are clamped to the last pixel and
   // the surplus steps are computed but not stored (branch-free steady state).
-  constexpr int PF = (NV * VW <= 4) ? 8 : ((NV * VW <= 6) ? 5 : 4);
+  constexpr int PF = SgmPf<NV, VW, PFSEL>::value;
   const LaneCtx cx = lv_ctx<NV, VW>(lane, min_limit);
   const long long pix0 = (long long)g.sy * W + g.sx;
   const long long step = (long long)g.dy * W + g.dx;
@@ -102,7 +121,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
       for (int k = 0; k < NV; ++k)
 #pragma unroll
         for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
-      lv_store<NV, VW, true>(o, optr, 0, dl);
+      if (store_vol) lv_store<NV, VW, true>(o, optr, 0, dl);
       if (WTA) lv_argmin_store<NV, VW>(o, lane, D, disp + pix0);
     } else {
       lv_store<NV, VW, true>(L, optr, 0, dl);
@@ -147,7 +166,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
           for (int k = 0; k < NV; ++k)
 #pragma unroll
             for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
-          lv_store<NV, VW, true>(o, optr, 0, dl);
+          if (store_vol) lv_store<NV, VW, true>(o, optr, 0, dl);
           if (WTA) lv_argmin_store<NV, VW>(o, lane, D, disp + pix0 + (long long)(i + u) * step);
         } else {
           lv_store<NV, VW, true>(L, optr, 0, dl);
@@ -173,25 +192,64 @@ __global__ void sgm_repeat_add_kernel(float *__restrict__ out, const float *__re
   out[pix * D + d] = s;
 }
 
+// Warps of one kernel variant that can be resident on the whole GPU at once (occupancy API).
+template <int NV, int VW, bool ACC, bool WTA, int PFSEL>
+static int resident_warps() {
+  static int cached = -1;  // per instantiation; a race would only recompute the same value
+  if (cached < 0) {
+    int nb = 0;
+    const int threads = SgmPf<NV, VW, PFSEL>::kThreads;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+            &nb, sgm_path_kernel<NV, VW, ACC, WTA, PFSEL>, threads, 0) != cudaSuccess) {
+      cudaGetLastError();
+      nb = 0;
+    }
+    cached = nb * (threads / 32) * num_sms();
+  }
+  return cached;
+}
+
+template <int NV, int VW, bool ACC, bool WTA, int PFSEL, typename... Args>
+static void launch_path_kernel(int path_count, cudaStream_t stream, Args... args) {
+  const int warps = SgmPf<NV, VW, PFSEL>::kThreads / 32;
+  const int blocks = (path_count + warps - 1) / warps;
+  sgm_path_kernel<NV, VW, ACC, WTA, PFSEL><<<blocks, warps * 32, 0, stream>>>(args...);
+}
+
+// One wave if possible: the deepest prefetch whose resident-warp capacity still holds every
+// path of the direction; the default when nothing fits (diagonals: many short paths, the
+// block scheduler balances them).  The result does not depend on the choice.
+template <int NV, int VW, bool ACC>
+static int pick_pfsel(int path_count) {
+  if (SgmPf<NV, VW, 1>::kHasDeep && path_count <= resident_warps<NV, VW, ACC, false, 1>()) return 1;
+  if (path_count <= resident_warps<NV, VW, ACC, false, 0>()) return 0;
+  if (SgmPf<NV, VW, 2>::kHasShallow && path_count <= resident_warps<NV, VW, ACC, false, 2>()) return 2;
+  return 0;
+}
+
 template <int NV, int VW>
 static int run_direction(const float *cost, const float *image, float *out, int H, int W, int D,
                          float p1, float p2, int dir, int path_begin, int path_count,
                          int min_limit, unsigned mode, float *l_store, int l_store_path,
                          cudaStream_t stream, int32_t *disp = nullptr) {
-  const int warps = 4;
-  const int blocks = (path_count + warps - 1) / warps;
-  if ((mode & kSgmEmitWta) && disp)  // last pass of the fused aggregate+reduce call
-    sgm_path_kernel<NV, VW, true, true><<<blocks, warps * 32, 0, stream>>>(
-        cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
-        l_store_path, disp);
-  else if (mode & kSgmAccumulate)
-    sgm_path_kernel<NV, VW, true, false><<<blocks, warps * 32, 0, stream>>>(
-        cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
-        l_store_path, nullptr);
-  else
-    sgm_path_kernel<NV, VW, false, false><<<blocks, warps * 32, 0, stream>>>(
-        cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, l_store,
-        l_store_path, nullptr);
+#define STM_SGM_ARGS cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, \
+                     l_store, l_store_path
+  if ((mode & kSgmEmitWta) && disp) {  // last pass of the fused aggregate+reduce call
+    launch_path_kernel<NV, VW, true, true, 0>(path_count, stream, STM_SGM_ARGS, disp);
+  } else if (mode & kSgmAccumulate) {
+    switch (pick_pfsel<NV, VW, true>(path_count)) {
+      case 1: launch_path_kernel<NV, VW, true, false, 1>(path_count, stream, STM_SGM_ARGS, nullptr); break;
+      case 2: launch_path_kernel<NV, VW, true, false, 2>(path_count, stream, STM_SGM_ARGS, nullptr); break;
+      default: launch_path_kernel<NV, VW, true, false, 0>(path_count, stream, STM_SGM_ARGS, nullptr);
+    }
+  } else {
+    switch (pick_pfsel<NV, VW, false>(path_count)) {
+      case 1: launch_path_kernel<NV, VW, false, false, 1>(path_count, stream, STM_SGM_ARGS, nullptr); break;
+      case 2: launch_path_kernel<NV, VW, false, false, 2>(path_count, stream, STM_SGM_ARGS, nullptr); break;
+      default: launch_path_kernel<NV, VW, false, false, 0>(path_count, stream, STM_SGM_ARGS, nullptr);
+    }
+  }
+#undef STM_SGM_ARGS
   return check_launch("sgm_path_kernel");
 }
 
@@ -221,7 +279,8 @@ static int sgm_by_direction(const float *cost, const float *image, float *out, i
     const int dir = order[pass];
     const int np = sgm_num_paths(dir, H, W);
     unsigned mode = (pass == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
-    if (disp && pass == 7) mode |= kSgmEmitWta;
+    if (disp && pass == 7)
+      mode |= kSgmEmitWta | ((flags & STM_SGM_DISPARITY_ONLY) ? kSgmSkipVolumeStore : 0u);
     const int multi = sgm_multi_path_index(dir, H, W);
     if (multi < 0) {
       rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, 0, np, min_limit, mode,
@@ -259,7 +318,8 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
   for (int dir = 0; dir < 8; ++dir) {
     const int np = sgm_num_paths(dir, H, W);
     unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
-    if (disp && dir == 7) mode |= kSgmEmitWta;  // portrait: direction 7 visits every pixel once
+    if (disp && dir == 7)  // portrait: direction 7 visits every pixel once
+      mode |= kSgmEmitWta | ((flags & STM_SGM_DISPARITY_ONLY) ? kSgmSkipVolumeStore : 0u);
     if (dir == 4) {
       const int multi = sgm_multi_path_index(5, H, W);
       const int times = sgm_path_geom(5, multi, H, W).mult - 1;
@@ -292,6 +352,17 @@ static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
 size_t sgm_workspace_bytes(int H, int W, int D) {
   const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_wave_workspace_bytes(H, W, D);
   return a > b ? a : b;
+}
+
+// Developer hook (tools/sgm_plan.py): resident-warp capacity of the D=128 variants and the
+// variant chosen for `paths` paths.  Not part of the ABI.
+extern "C" __attribute__((visibility("default"))) void stm_debug_sgm_plan(int paths, int *out6) {
+  out6[0] = resident_warps<1, 4, true, false, 0>();
+  out6[1] = resident_warps<1, 4, true, false, 1>();
+  out6[2] = resident_warps<1, 4, true, false, 2>();
+  out6[3] = pick_pfsel<1, 4, true>(paths);
+  out6[4] = pick_pfsel<1, 4, false>(paths);
+  out6[5] = num_sms();
 }
 
 int launch_sgm(const float *cost, const float *image, float *out, int H, int W, int D, float p1,

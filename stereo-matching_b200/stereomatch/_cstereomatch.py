@@ -21,6 +21,7 @@ _LIB_PATH = Path(__file__).resolve().parent / "libstm_b200.so"
 STM_SGM_MIN_ALL_D = 1
 STM_SGM_OVERWRITE = 2
 STM_SGM_FUSED_SWEEPS = 4
+STM_SGM_DISPARITY_ONLY = 8
 STM_DP_CPU_EXACT = 1
 
 if not _LIB_PATH.exists():

@@ -4,7 +4,8 @@ from typing import Optional
 import torch
 
 from ._common import empty_tensor
-from ._cstereomatch import STM_SGM_MIN_ALL_D, STM_SGM_OVERWRITE, STM_SGM_FUSED_SWEEPS
+from ._cstereomatch import (STM_SGM_MIN_ALL_D, STM_SGM_OVERWRITE, STM_SGM_FUSED_SWEEPS,
+                             STM_SGM_DISPARITY_ONLY)
 from ._cstereomatch import AggregationOps as _AggregationOps
 
 
@@ -46,17 +47,21 @@ class Semiglobal:
 
     def aggregate_and_reduce(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
                              sga_volume: Optional[torch.Tensor] = None,
-                             disparity_img: Optional[torch.Tensor] = None):
+                             disparity_img: Optional[torch.Tensor] = None, keep_volume: bool = True):
         """New: aggregation followed by winner-takes-all in one native call; returns
         (sga_volume, disparity_img).  The argmin is taken inside the last aggregation pass, so
         the aggregated volume is not re-read; that pass must visit every pixel once, hence the
         last two directions run in swapped order and sga_volume equals __call__'s result up to
-        fp32 association.  The disparity map is exactly WinnerTakesAll()(sga_volume)."""
+        fp32 association.  The disparity map is exactly WinnerTakesAll()(sga_volume).
+        keep_volume=False: sga_volume is only scratch (the last pass does not write the sums
+        back, 4 B/pix-disp less traffic); the returned volume is then NOT the aggregation."""
         sga_volume = empty_tensor(*cost_volume.size(), dtype=cost_volume.dtype,
                                   device=cost_volume.device, reuse_tensor=sga_volume)
         disparity_img = empty_tensor(cost_volume.size(0), cost_volume.size(1), dtype=torch.int32,
                                      device=cost_volume.device, reuse_tensor=disparity_img)
         flags = STM_SGM_OVERWRITE | (STM_SGM_MIN_ALL_D if self.min_over_all_d else 0)
+        if not keep_volume:
+            flags |= STM_SGM_DISPARITY_ONLY
         _AggregationOps.run_semiglobal_wta(cost_volume, left_image, self.penalty1, self.penalty2,
                                            sga_volume, disparity_img, flags)
         return sga_volume, disparity_img

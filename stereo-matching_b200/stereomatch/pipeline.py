@@ -26,6 +26,10 @@ class Pipeline:
         # New: Semiglobal followed by WinnerTakesAll runs as one native call (the argmin is
         # folded into the last aggregation pass).  Set to False for two separate stages.
         self.fuse_aggregation_and_reduce = True
+        # The aggregated volume never leaves the pipeline, so the fused call may skip writing it
+        # (its buffer is scratch then).  Set to True to find the aggregation in
+        # `_aggregation_volume` after estimate().
+        self.keep_aggregation_volume = False
 
     def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor) -> torch.Tensor:
         """[H,W] left/right images (CUDA float32) -> int32 [H,W] disparity map."""
@@ -38,7 +42,7 @@ class Pipeline:
                     and type(self.aggregation) is Semiglobal and not self.aggregation.fused_sweeps):
                 self._aggregation_volume, self._disparity_image = self.aggregation.aggregate_and_reduce(
                     self._cost_volume, left_image.to(self._cost_volume.device), own,
-                    self._disparity_image)
+                    self._disparity_image, keep_volume=self.keep_aggregation_volume)
                 return self._disparity_image
             self._aggregation_volume = self.aggregation(
                 self._cost_volume, left_image.to(self._cost_volume.device), own)

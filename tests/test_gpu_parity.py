@@ -288,6 +288,11 @@ def test_sgm_with_wta_folded_into_the_last_pass(sm, H, W, D, kind):
     # buffers are reused when passed back in
     vol2, disp2 = sgm.aggregate_and_reduce(c, l, vol, disp)
     assert vol2.data_ptr() == vol.data_ptr() and disp2.data_ptr() == disp.data_ptr()
+    # STM_SGM_DISPARITY_ONLY: the last pass does not write the sums back; same disparity map
+    want = disp.clone()
+    scratch, disp3 = sgm.aggregate_and_reduce(c, l, keep_volume=False)
+    assert torch.equal(disp3, want)
+    assert not torch.equal(scratch, vol)      # the volume really was left unfinished
 
 
 def test_sgm_wta_fold_argmin_rule_with_nan_and_inf(sm):
@@ -317,6 +322,10 @@ def test_pipeline_fused_and_unfused_agree(sm):
     plain.fuse_aggregation_and_reduce = False
     a, b = fused.estimate(l, r), plain.estimate(l, r)
     assert float((a != b).float().mean()) <= 1e-3   # north_star: <= 0.1 % of pixels
+    keep = mk()
+    keep.keep_aggregation_volume = True             # default False: the volume is scratch
+    assert torch.equal(keep.estimate(l, r), a)
+    assert torch.equal(sm.disparity_reduce.WinnerTakesAll()(keep._aggregation_volume), a)
     want = O.wta(O.sgm(O.ssd(left, right, D, 7), left, 0.1, 0.2))
     assert float((a.cpu().numpy() != want).mean()) <= 1e-3
     assert float((b.cpu().numpy() != want).mean()) <= 1e-3
