@@ -17,12 +17,16 @@
 // order-preserving integer keys.  The next pixel's cost vector is prefetched while the
 // current one is being reduced.
 #include "lanevec.cuh"
+#include <cstdlib>
+#include <cstring>
+
 #include "sgm_paths.cuh"
 
 namespace stm {
 
 enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u, kSgmEmitWta = 8u,
-                  kSgmSkipVolumeStore = 16u /* with kSgmEmitWta: the sum is reduced, not written */ };
+                  kSgmSkipVolumeStore = 16u /* with kSgmEmitWta: the sum is reduced, not written */,
+                  kSgmReverseOrder = 32u /* warps take the paths of the direction last to first */ };
 
 // Winner-takes-all of one pixel's vector held across the warp, with the rule of wta.cu /
 // reference src/winners_take_all.cu:21-40: first (lowest-d) minimum, all-inf -> 0, NaN never
@@ -80,7 +84,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
   const int lane = threadIdx.x & 31;
   const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (w >= path_count) return;
-  const int path = path_begin + w;
+  const int path = path_begin + ((mode & kSgmReverseOrder) ? path_count - 1 - w : w);
   const PathGeom g = sgm_path_geom(dir, path, H, W);
   if (g.mult == 0) return;
   const bool write_out = !(mode & kSgmNoOutput);
@@ -94,6 +98,7 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
   // whole groups of PF pixels: prefetches past the end are clamped to the last pixel and
   // the surplus steps are computed but not stored (branch-free steady state).
   constexpr int PF = SgmPf<NV, VW, PFSEL>::value;
+  constexpr int RB = (PFSEL == 1 && SgmPf<NV, VW, PFSEL>::kHasDeep) ? 4 : 1;  // refill batch
   const LaneCtx cx = lv_ctx<NV, VW>(lane, min_limit);
   const long long pix0 = (long long)g.sy * W + g.sx;
   const long long step = (long long)g.dy * W + g.dx;
@@ -149,11 +154,17 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
       LaneVec<NV, VW> o;
       if (ACC) o = sbuf[u];
       const float intensity = ibuf[u];
-      // refill slot u with pixel i+u+PF (clamped)
-      if (left > 0) { cfetch += step_d; sfetch += step_d; ifetch += step; --left; }
-      lv_load<NV, VW, true>(cbuf[u], cfetch, 0, dl);
-      if (ACC) lv_load<NV, VW, true>(sbuf[u], sfetch, 0, dl);
-      ibuf[u] = __ldg(ifetch);
+      // refill with pixel i+u+PF (clamped): slot u at once, or RB consumed slots together so
+      // that one warp asks for RB consecutive pixels (RB*D*4 contiguous bytes) back to back
+      if ((u + 1) % RB == 0) {
+#pragma unroll
+        for (int b = u + 1 - RB; b <= u; ++b) {
+          if (left > 0) { cfetch += step_d; sfetch += step_d; ifetch += step; --left; }
+          lv_load<NV, VW, true>(cbuf[b], cfetch, 0, dl);
+          if (ACC) lv_load<NV, VW, true>(sbuf[b], sfetch, 0, dl);
+          ibuf[b] = __ldg(ifetch);
+        }
+      }
 
       lv_sgm_step<NV, VW>(L, c, p1, sgm_p2_adjusted(p1, p2, intensity, prev_intensity), cx);
       prev_intensity = intensity;
@@ -227,6 +238,19 @@ static int pick_pfsel(int path_count) {
   return 0;
 }
 
+// Developer knob: STM_DEBUG_SGM_PFSEL="01220000" forces the variant per direction ('-' = auto).
+static int pfsel_override(int dir) {
+  static int tbl[8];
+  static bool init = false;
+  if (!init) {
+    const char *e = getenv("STM_DEBUG_SGM_PFSEL");
+    const bool ok = e && strlen(e) == 8;
+    for (int i = 0; i < 8; ++i) tbl[i] = (ok && e[i] >= '0' && e[i] <= '2') ? e[i] - '0' : -1;
+    init = true;
+  }
+  return tbl[dir & 7];
+}
+
 template <int NV, int VW>
 static int run_direction(const float *cost, const float *image, float *out, int H, int W, int D,
                          float p1, float p2, int dir, int path_begin, int path_count,
@@ -234,16 +258,30 @@ static int run_direction(const float *cost, const float *image, float *out, int 
                          cudaStream_t stream, int32_t *disp = nullptr) {
 #define STM_SGM_ARGS cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, \
                      l_store, l_store_path
+  const int ov = pfsel_override(dir);
+  {
+    // Launch order of a direction's paths (the result does not depend on it).  The paths of a
+    // diagonal that start on the top/bottom edge advance through the image rows together, so
+    // the resident warps read contiguous memory; those that start on the left/right edge are
+    // each in a row of their own.  Starting with the row-synchronous set is ~80 us faster at
+    // 1080p (measured, profiles/r01_v10_sgm_order_sweep.txt): direction 4 enumerates its
+    // left-edge paths first, so it is taken last to first; 5, 6, 7 are fine as they are.
+    static const char *flip = getenv("STM_DEBUG_SGM_FLIP");  // developer knob, 8 x '0'/'1'
+    const bool dflt = dir == 4;
+    const bool rev = (flip && strlen(flip) == 8) ? flip[dir & 7] == '1' : dflt;
+    if (rev) mode |= kSgmReverseOrder;
+  }
   if ((mode & kSgmEmitWta) && disp) {  // last pass of the fused aggregate+reduce call
-    launch_path_kernel<NV, VW, true, true, 0>(path_count, stream, STM_SGM_ARGS, disp);
+    if (ov == 2) launch_path_kernel<NV, VW, true, true, 2>(path_count, stream, STM_SGM_ARGS, disp);
+    else launch_path_kernel<NV, VW, true, true, 0>(path_count, stream, STM_SGM_ARGS, disp);
   } else if (mode & kSgmAccumulate) {
-    switch (pick_pfsel<NV, VW, true>(path_count)) {
+    switch (ov >= 0 ? ov : pick_pfsel<NV, VW, true>(path_count)) {
       case 1: launch_path_kernel<NV, VW, true, false, 1>(path_count, stream, STM_SGM_ARGS, nullptr); break;
       case 2: launch_path_kernel<NV, VW, true, false, 2>(path_count, stream, STM_SGM_ARGS, nullptr); break;
       default: launch_path_kernel<NV, VW, true, false, 0>(path_count, stream, STM_SGM_ARGS, nullptr);
     }
   } else {
-    switch (pick_pfsel<NV, VW, false>(path_count)) {
+    switch (ov >= 0 ? ov : pick_pfsel<NV, VW, false>(path_count)) {
       case 1: launch_path_kernel<NV, VW, false, false, 1>(path_count, stream, STM_SGM_ARGS, nullptr); break;
       case 2: launch_path_kernel<NV, VW, false, false, 2>(path_count, stream, STM_SGM_ARGS, nullptr); break;
       default: launch_path_kernel<NV, VW, false, false, 0>(path_count, stream, STM_SGM_ARGS, nullptr);
