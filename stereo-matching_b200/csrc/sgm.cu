@@ -238,6 +238,10 @@ static int pick_pfsel(int path_count) {
   return 0;
 }
 
+// sgm_row.cu
+int launch_sgm_row(const float *, const float *, float *, int, int, int, float, float, int, int,
+                   bool, cudaStream_t);
+
 // Developer knob: STM_DEBUG_SGM_PFSEL="01220000" forces the variant per direction ('-' = auto).
 static int pfsel_override(int dir) {
   static int tbl[8];
@@ -258,6 +262,12 @@ static int run_direction(const float *cost, const float *image, float *out, int 
                          cudaStream_t stream, int32_t *disp = nullptr) {
 #define STM_SGM_ARGS cost, image, out, H, W, D, p1, p2, dir, path_begin, path_count, min_limit, mode, \
                      l_store, l_store_path
+  // horizontal directions: tiles staged through shared memory by bulk copies (sgm_row.cu)
+  if (dir <= 1 && path_begin == 0 && !(mode & (kSgmStoreL | kSgmNoOutput | kSgmEmitWta))) {
+    const int rc = launch_sgm_row(cost, image, out, H, W, D, p1, p2, dir, min_limit,
+                                  (mode & kSgmAccumulate) != 0, stream);
+    if (rc != 1) return rc;
+  }
   const int ov = pfsel_override(dir);
   {
     // Launch order of a direction's paths (the result does not depend on it).  The paths of a

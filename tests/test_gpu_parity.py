@@ -133,6 +133,25 @@ def test_sgm_vs_oracle(sm, H, W, D, scale, p1, p2, all_d, fused_sweeps):
     assert_volume_close(got, want)
 
 
+@pytest.mark.parametrize("H,W,D", [(4, 8, 128), (4, 2, 128), (5, 16, 128), (3, 25, 128), (6, 64, 256),
+                                     (5, 19, 512), (7, 24, 320), (3, 17, 448), (9, 31, 160)])
+def test_sgm_horizontal_bulk_copy_kernel_tiles(sm, H, W, D):
+    """csrc/sgm_row.cu (directions 0 and 1 for D % 32 == 0): every tile size (8, 4, 2 pixels),
+    widths that are a multiple of the tile, one more, one tile, less than a tile; rows beyond
+    the last CTA's image rows (H % 4 != 0)."""
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 11 + W, scale="unit")
+    cost = synth.random_volume(H, W, D, seed=D + W, hi=3.0)
+    want = O.sgm(cost, left, 0.1, 0.2)
+    c, l = cuda(cost), cuda(left)
+    got = sm.aggregation.Semiglobal()(c, l)
+    assert_volume_close(got, want)
+    # the raw op accumulates: direction 0 then runs the read-modify-write variant too
+    from stereomatch._cstereomatch import AggregationOps
+    acc = torch.zeros_like(got)
+    AggregationOps.run_semiglobal(c, l, 0.1, 0.2, acc)
+    assert torch.equal(acc, got)            # 0 + L is exact, the rest is the same sequence
+
+
 @pytest.mark.parametrize("H,W,D", [(70, 150, 128), (150, 70, 64), (45, 333, 192), (33, 100, 32),
                                      (64, 64, 128), (5, 700, 64), (130, 9, 16)])
 def test_sgm_sweeps_many_ctas_and_ring_wraps(sm, H, W, D):
