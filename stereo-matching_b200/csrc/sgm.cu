@@ -68,9 +68,10 @@ template <int NV, int VW, int PFSEL>
 struct SgmPf {
   static constexpr int kBase = (NV * VW <= 4) ? 8 : ((NV * VW <= 6) ? 5 : 4);
   static constexpr bool kHasDeep = NV * VW <= 4;     // larger vectors would spill at twice the depth
-  static constexpr bool kHasShallow = NV * VW <= 4;  // larger vectors cannot get under 128 registers
+  static constexpr bool kHasShallow = NV * VW <= 8;  // larger vectors cannot get under 128 registers
+  static constexpr int kShallow = (NV * VW <= 4) ? 5 : ((NV * VW <= 6) ? 3 : 2);
   static constexpr int value = (PFSEL == 1 && kHasDeep) ? 2 * kBase
-                               : ((PFSEL == 2 && kHasShallow) ? 5 : kBase);
+                               : ((PFSEL == 2 && kHasShallow) ? kShallow : kBase);
   static constexpr int kThreads = 128;
   static constexpr int kMinBlocks = (PFSEL == 2 && kHasShallow) ? 4 : 0;  // 0 = unspecified
 };
