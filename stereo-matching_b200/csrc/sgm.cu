@@ -189,6 +189,116 @@ sgm_path_kernel(const float *__restrict__ cost, const float *__restrict__ image,
   }
 }
 
+// Diagonal directions (4..7) of a landscape or square image as a ROW-SYNCHRONOUS sweep.
+// Warp w is a column slot: at step i it is at row y = (dy > 0 ? i : H-1-i), column
+// (w + dx*i) mod W.  A slot that leaves the image on one side re-enters on the other, where a
+// new path of the same direction begins (L = C there); with W >= H that happens at most once
+// per slot.  Same paths, same arithmetic and same per-pixel accumulation as sgm_path_kernel --
+// only the assignment of paths to warps differs:
+//  * every active warp does exactly H steps (one-path-per-warp gives lengths 1..H, and the
+//    pass ends with a few long chains running alone at next to no bandwidth);
+//  * all warps are on the same image row at the same time, so together they read whole
+//    contiguous rows (the pattern that streams at ~6.6 TB/s) instead of 983-KB-strided pieces;
+//  * for the defective up-diagonals (5, 7) a slot is either active in both of
+//    its paths or in neither, so the skipped band costs nothing: idle slots exit at once.
+template <int NV, int VW, int PFSEL>
+__global__ void __launch_bounds__(SgmPf<NV, VW, PFSEL>::kThreads, SgmPf<NV, VW, PFSEL>::kMinBlocks)
+sgm_diag_rows_kernel(const float *__restrict__ cost, const float *__restrict__ image,
+                     float *__restrict__ out, int H, int W, int D, float p1, float p2, int dir,
+                     int min_limit, unsigned mode, float *__restrict__ l_store, int l_store_path) {
+  const int lane = threadIdx.x & 31;
+  const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (w >= W) return;
+  const int dx = (dir == 4 || dir == 7) ? 1 : -1;
+  const int dy = (dir == 4 || dir == 6) ? 1 : -1;
+  // the path this slot is on at step 0 (it starts on the top or bottom row at column w)
+  const int idx0 = (dir == 4 || dir == 7) ? w + H - 1 : w;
+  if (sgm_path_geom(dir, idx0, H, W).mult == 0) return;  // slot inside the skipped band
+  const bool store_l = (mode & kSgmStoreL) && idx0 == l_store_path;
+  constexpr int dpad = NV * 32 * VW;
+  constexpr int PF = SgmPf<NV, VW, PFSEL>::value;
+  const LaneCtx cx = lv_ctx<NV, VW>(lane, min_limit);
+
+  const int n = H;
+  const int iw = dx > 0 ? W - w : w + 1;  // first step on the slot's second path (>= H: none)
+  const long long step = (long long)dy * W + dx;
+  const long long wrap = -(long long)dx * W;  // added to `step` when the column wraps
+  const long long pix0 = (long long)(dy > 0 ? 0 : H - 1) * W + w;
+  const int lane_off = lane * VW;
+  const float *cfetch = cost + pix0 * D + lane_off;
+  const float *sfetch = out + pix0 * D + lane_off;
+  const float *ifetch = image + pix0;
+  float *optr = out + pix0 * D + lane_off;
+  float *lptr = l_store + lane_off;
+  const int dl = D - lane_off;
+
+  // step 0: L = C
+  LaneVec<NV, VW> L;
+  lv_load<NV, VW, true>(L, cfetch, 0, dl);
+  float prev_intensity = __ldg(ifetch);
+  {
+    LaneVec<NV, VW> o;
+    lv_load<NV, VW, true>(o, sfetch, 0, dl);
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+    lv_store<NV, VW, true>(o, optr, 0, dl);
+  }
+  if (store_l) lv_store<NV, VW, false>(L, lptr, 0, dpad);
+  if (n == 1) return;
+
+  LaneVec<NV, VW> cbuf[PF], sbuf[PF];
+  float ibuf[PF];
+  int left = n - 1;    // pixels not yet fetched
+  int fnext = 1;       // step index the fetch pointers move to next
+  auto advance_fetch = [&]() {  // pointer arithmetic only: no load sits under this branch
+    if (left > 0) {
+      const long long adv = step + (fnext == iw ? wrap : 0);
+      cfetch += adv * D; sfetch += adv * D; ifetch += adv;
+      ++fnext; --left;
+    }
+  };
+#pragma unroll
+  for (int u = 0; u < PF; ++u) {
+    advance_fetch();
+    lv_load<NV, VW, true>(cbuf[u], cfetch, 0, dl);
+    lv_load<NV, VW, true>(sbuf[u], sfetch, 0, dl);
+    ibuf[u] = __ldg(ifetch);
+  }
+
+  for (int i = 1; i < n; i += PF) {
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+      const LaneVec<NV, VW> c = cbuf[u];
+      LaneVec<NV, VW> o = sbuf[u];
+      const float intensity = ibuf[u];
+      advance_fetch();
+      lv_load<NV, VW, true>(cbuf[u], cfetch, 0, dl);
+      lv_load<NV, VW, true>(sbuf[u], sfetch, 0, dl);
+      ibuf[u] = __ldg(ifetch);
+
+      const int cur = i + u;
+      if (cur == iw) {
+        L = c;  // the slot re-entered the image: first pixel of its second path
+      } else {
+        lv_sgm_step<NV, VW>(L, c, p1, sgm_p2_adjusted(p1, p2, intensity, prev_intensity), cx);
+      }
+      prev_intensity = intensity;
+      optr += (step + (cur == iw ? wrap : 0)) * D;
+      lptr += dpad;
+      if (cur < n) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+        lv_store<NV, VW, true>(o, optr, 0, dl);
+        if (store_l) lv_store<NV, VW, false>(L, lptr, 0, dpad);
+      }
+    }
+  }
+}
+
 // Adds the stored path vector `times` more times, one fp32 addition at a time exactly as
 // the reference does when it re-runs the corner diagonal.
 __global__ void sgm_repeat_add_kernel(float *__restrict__ out, const float *__restrict__ l_store,
@@ -256,6 +366,42 @@ static int pfsel_override(int dir) {
   return tbl[dir & 7];
 }
 
+// Row-synchronous diagonal pass (sgm_diag_rows_kernel): W slots; `busy` of them do H steps.
+template <int NV, int VW, int PFSEL>
+static int diag_rows_resident() {
+  static int cached = -1;
+  if (cached < 0) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, sgm_diag_rows_kernel<NV, VW, PFSEL>,
+                                                      SgmPf<NV, VW, PFSEL>::kThreads, 0) != cudaSuccess) {
+      cudaGetLastError();
+      nb = 0;
+    }
+    cached = nb * (SgmPf<NV, VW, PFSEL>::kThreads / 32) * num_sms();
+  }
+  return cached;
+}
+
+// Returns 1 when the pass is better left to sgm_path_kernel.  Measured at 1080p D=128
+// (profiles/r01_v13_sgm_diag_rows.txt): with one slot per column the full diagonals (4, 6) are
+// no faster than one warp per path (503 vs 495 us), and the defective ones (5, 7; H busy slots)
+// only win with 16 pixels in flight per warp (355 vs 365 us; 410 us at depth 8) -- with so few
+// warps the bytes in flight per warp decide, not the balance.  So: directions 5 and 7, and only
+// when the deep variant exists for the lane map and all busy slots are resident at once.
+template <int NV, int VW>
+static int run_diag_rows(const float *cost, const float *image, float *out, int H, int W, int D,
+                         float p1, float p2, int dir, int min_limit, unsigned mode, float *l_store,
+                         int l_store_path, cudaStream_t stream) {
+  if (dir != 5 && dir != 7) return 1;
+  if (!SgmPf<NV, VW, 1>::kHasDeep) return 1;
+  const int busy = H + 1;  // the other W-H-1 slots lie in the skipped band and exit at once
+  if (busy > diag_rows_resident<NV, VW, 1>()) return 1;
+  const int warps = 4, blocks = (W + warps - 1) / warps;
+  sgm_diag_rows_kernel<NV, VW, 1><<<blocks, warps * 32, 0, stream>>>(
+      cost, image, out, H, W, D, p1, p2, dir, min_limit, mode, l_store, l_store_path);
+  return check_launch("sgm_diag_rows_kernel");
+}
+
 template <int NV, int VW>
 static int run_direction(const float *cost, const float *image, float *out, int H, int W, int D,
                          float p1, float p2, int dir, int path_begin, int path_count,
@@ -268,6 +414,16 @@ static int run_direction(const float *cost, const float *image, float *out, int 
     const int rc = launch_sgm_row(cost, image, out, H, W, D, p1, p2, dir, min_limit,
                                   (mode & kSgmAccumulate) != 0, stream);
     if (rc != 1) return rc;
+  }
+  // diagonal directions of landscape / square images: row-synchronous slots
+  if (dir >= 4 && W >= H && H >= 2 && path_begin == 0 && (mode & kSgmAccumulate) &&
+      !(mode & (kSgmNoOutput | kSgmEmitWta))) {
+    static const char *off = getenv("STM_DEBUG_SGM_DIAG_ROWS");  // developer knob: "0" disables
+    if (!(off && off[0] == '0')) {
+      const int rc = run_diag_rows<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, min_limit, mode,
+                                           l_store, l_store_path, stream);
+      if (rc != 1) return rc;
+    }
   }
   const int ov = pfsel_override(dir);
   {
