@@ -261,6 +261,17 @@ def run_b200_arm(args):
     sgm_launches = C.launch_count() - sgm_launches0
     torch.cuda.synchronize()
 
+    # every direction pass of the dominant stage on its own: CUDA events recorded by the
+    # library on the launching stream around each pass (stm_sgm_pass_timing)
+    pass_ms = {}
+    C.AggregationOps.pass_timing(True)
+    for rep in range(reps):
+        l, r = dev_frames[rep % F]
+        sgm(cost, l, pipe._aggregation_volume)
+        for k, (d, t) in enumerate(C.AggregationOps.last_pass_ms()):
+            pass_ms.setdefault((k, d), []).append(t)
+    C.AggregationOps.pass_timing(False)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -280,6 +291,12 @@ def run_b200_arm(args):
             traffic = json.loads(tp.read_text()).get(dom)
         except Exception:
             traffic = None
+    passes = []
+    for (k, d), ts in sorted(pass_ms.items()):
+        t = sorted(ts)[len(ts) // 2]
+        b = sgm_pass_bytes(d, k == 0, H, W, D)
+        passes.append({"dir": d, "ms": round(t, 4), "bytes": b, "GBs": round(b / (t * 1e-3) / 1e9, 1),
+                       "frac_of_peak": round(b / (t * 1e-3) / 1e9 / peak, 3)})
     stages = {k: {"ms": round(v, 4), "algo_GBs": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9, 1),
                   "frac": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9 / peak, 4)}
               for k, v in stage_ms.items()}
@@ -307,7 +324,10 @@ def run_b200_arm(args):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": f"{dom} stage ({sgm_launches} launches)" if dom == "sgm" else dom,
                      "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": traffic},
+                     "frac": achieved / peak, "traffic": traffic,
+                     # what each launch of the per-direction design HAS to move (C read, S
+                     # read-modify-write; the first pass only writes) over its own duration
+                     "passes": passes},
         "stages": stages,
         "cpu_baseline": cpu_baseline,
     }
@@ -315,6 +335,23 @@ def run_b200_arm(args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def sgm_pass_bytes(direction, first, H, W, D):
+    """Bytes one direction pass must move in the per-direction design: read C, read and write
+    S (the first pass only writes S), read the intensity, for the pixels the direction visits
+    (the defective up-diagonals 5 and 7 skip a band of a landscape image)."""
+    import numpy as np
+    y, x = np.mgrid[0:H, 0:W]
+    active = np.ones((H, W), dtype=bool)
+    if direction == 5 and W != H:
+        c, cs = x - y, W - H
+        active = ~((c >= 0) & (c < cs)) if W > H else ~((c > cs) & (c <= -1))
+    elif direction == 7 and W > H:
+        s_ = x + y
+        active = ~((s_ >= H) & (s_ <= W - 1))
+    px = int(active.sum())
+    return px * D * 4 * (2 if first else 3) + px * 4
 
 
 def main():

@@ -99,6 +99,15 @@ int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *d
                     int W, int D, float penalty1, float penalty2, unsigned flags, void *workspace,
                     size_t workspace_bytes, void *stream);
 
+/* Measurement API (new; bench.py's per-pass roofline lines).  With timing enabled, every
+ * stm_sgm_f32 / stm_sgm_wta_f32 call records CUDA events on its stream around each of the
+ * eight direction passes (a pass = the direction's kernel plus its corner-diagonal replay, see
+ * SURVEY.md F5).  stm_sgm_last_pass_ms waits for the last call's final event and returns the
+ * number of passes (8; 0 if no call was timed), filling ms[i] and directions[i] in launch
+ * order.  Process-wide state, not thread-safe: a measurement switch, not a product feature. */
+int stm_sgm_pass_timing(int enable);
+int stm_sgm_last_pass_ms(float *ms, int *directions, int capacity);
+
 /* Replaces DisparityReduceOps.run_winners_take_all(cost, disparity)
  * (reference src/disparity_reduce.cpp:6-9 -> RunWinnersTakeAll, src/winners_take_all.cu:89-114).
  * CPU rule: first (lowest-d) minimum, all-inf -> 0, NaN never wins.  Any D >= 1. */

@@ -17,6 +17,8 @@ int launch_wta(const float *, int32_t *, int, int, int, cudaStream_t);
 int launch_ssd(const float *, const float *, float *, int, int, int, int, cudaStream_t);
 int launch_birchfield(const float *, const float *, float *, int, int, int, cudaStream_t);
 size_t sgm_workspace_bytes(int, int, int);
+int sgm_pass_timing(bool);
+int sgm_last_pass_ms(float *, int *, int);
 int launch_sgm(const float *, const float *, float *, int, int, int, float, float, unsigned, void *,
                size_t, cudaStream_t, int32_t *disp = nullptr);
 int launch_dp(const float *, int8_t *, float *, int32_t *, int, int, int, unsigned, cudaStream_t);
@@ -120,6 +122,13 @@ int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *d
   if ((rc = require_device())) return rc;
   return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace, workspace_bytes,
                     (cudaStream_t)stream, disparity);
+}
+
+int stm_sgm_pass_timing(int enable) { return sgm_pass_timing(enable != 0); }
+
+int stm_sgm_last_pass_ms(float *ms, int *directions, int capacity) {
+  STM_REQUIRE(ms && directions, "sgm_last_pass_ms: null pointer");
+  return sgm_last_pass_ms(ms, directions, capacity);
 }
 
 int stm_wta_f32(const float *cost, int32_t *disparity, int H, int W, int D, void *stream) {

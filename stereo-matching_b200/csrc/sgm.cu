@@ -467,6 +467,46 @@ int sgm_repeat_add(float *out, float *l_store, int H, int W, int D, int dpad, in
   return check_launch("sgm_repeat_add_kernel");
 }
 
+// ---- per-pass timing (measurement API, include/stm_abi.h: stm_sgm_pass_timing) -------------
+// CUDA events on the launching stream around each direction's launches (its corner-diagonal
+// replay included), so bench.py can report every pass against the roofline without a profiler.
+static bool g_pass_timing = false;
+static cudaEvent_t g_pass_ev[9];
+static bool g_pass_ev_ready = false;
+static int g_pass_dirs[8];
+static int g_pass_count = 0;
+
+int sgm_pass_timing(bool enable) {
+  if (enable && !g_pass_ev_ready) {
+    for (int i = 0; i < 9; ++i)
+      if (cudaEventCreate(&g_pass_ev[i]) != cudaSuccess) return fail(STM_ECUDA, "sgm: cudaEventCreate failed");
+    g_pass_ev_ready = true;
+  }
+  g_pass_timing = enable;
+  g_pass_count = 0;
+  return STM_OK;
+}
+
+int sgm_last_pass_ms(float *ms, int *dirs, int capacity) {
+  if (g_pass_count == 0) return 0;
+  if (capacity < g_pass_count) return fail(STM_EINVAL, "sgm: pass buffer too small");
+  if (cudaEventSynchronize(g_pass_ev[g_pass_count]) != cudaSuccess)
+    return fail(STM_ECUDA, "sgm: cudaEventSynchronize failed");
+  for (int i = 0; i < g_pass_count; ++i) {
+    if (cudaEventElapsedTime(&ms[i], g_pass_ev[i], g_pass_ev[i + 1]) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: cudaEventElapsedTime failed");
+    dirs[i] = g_pass_dirs[i];
+  }
+  return g_pass_count;
+}
+
+static inline void pass_mark(int pass, int dir, cudaStream_t stream) {
+  if (!g_pass_timing) return;
+  cudaEventRecord(g_pass_ev[pass], stream);
+  if (pass < 8) g_pass_dirs[pass] = dir;
+  g_pass_count = pass;  // number of complete intervals so far
+}
+
 template <int NV, int VW>
 static int sgm_by_direction(const float *cost, const float *image, float *out, int H, int W,
                             int D, float p1, float p2, unsigned flags, float *ws,
@@ -482,6 +522,7 @@ static int sgm_by_direction(const float *cost, const float *image, float *out, i
   const int *order = disp ? fused : plain;
   for (int pass = 0; pass < 8; ++pass) {
     const int dir = order[pass];
+    pass_mark(pass, dir, stream);
     const int np = sgm_num_paths(dir, H, W);
     unsigned mode = (pass == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
     if (disp && pass == 7)
@@ -505,6 +546,7 @@ static int sgm_by_direction(const float *cost, const float *image, float *out, i
       if (rc) return rc;
     }
   }
+  pass_mark(8, -1, stream);
   return STM_OK;
 }
 
@@ -521,6 +563,7 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
   const int dpad = NV * 32 * VW;
   int rc;
   for (int dir = 0; dir < 8; ++dir) {
+    pass_mark(dir, dir, stream);
     const int np = sgm_num_paths(dir, H, W);
     unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
     if (disp && dir == 7)  // portrait: direction 7 visits every pixel once
@@ -540,6 +583,7 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
                                nullptr, -1, stream, disp);
     if (rc) return rc;
   }
+  pass_mark(8, -1, stream);
   return STM_OK;
 }
 

@@ -43,6 +43,8 @@ _lib.stm_sgm_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _f, _f, _u, _vp, _sz, _v
 _lib.stm_wta_f32.argtypes = [_vp, _vp, _i, _i, _i, _vp]
 _lib.stm_sgm_wta_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _u, _vp, _sz, _vp]
 _lib.stm_dp_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _u, _vp]
+_lib.stm_sgm_pass_timing.argtypes = [_i]
+_lib.stm_sgm_last_pass_ms.argtypes = [_vp, _vp, _i]
 _lib.stm_pipeline_host_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _u, _i, _u]
 for _name in ("stm_ssd_f32", "stm_birchfield_f32", "stm_sgm_f32", "stm_sgm_wta_f32", "stm_wta_f32",
               "stm_dp_f32", "stm_pipeline_host_f32"):
@@ -153,6 +155,22 @@ class AggregationOps:
                                     float(penalty1), float(penalty2), int(flags), ws.data_ptr(),
                                     ws.numel(), _stream()))
 
+
+    @staticmethod
+    def pass_timing(enable: bool) -> None:
+        """New (measurement): record CUDA events around each direction pass of the following
+        run_semiglobal / run_semiglobal_wta calls (include/stm_abi.h, stm_sgm_pass_timing)."""
+        _check(_lib.stm_sgm_pass_timing(1 if enable else 0))
+
+    @staticmethod
+    def last_pass_ms():
+        """[(direction, milliseconds)] of the last timed call, in launch order; waits for it."""
+        ms = (ctypes.c_float * 8)()
+        dirs = (ctypes.c_int * 8)()
+        n = _lib.stm_sgm_last_pass_ms(ms, dirs, 8)
+        if n < 0:
+            _check(n)
+        return [(int(dirs[i]), float(ms[i])) for i in range(n)]
 
     @staticmethod
     def run_semiglobal_wta(cost_volume, left_image, penalty1: float, penalty2: float,

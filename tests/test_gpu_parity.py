@@ -183,6 +183,31 @@ def test_sgm_accumulates_like_the_reference(sm):
     assert_volume_close(out, want)
 
 
+def test_sgm_pass_timing_api(sm):
+    """stm_sgm_pass_timing / stm_sgm_last_pass_ms: eight passes in launch order with positive
+    durations (reference order for the plain call, 6 and 7 swapped when WTA is folded in),
+    nothing when disabled, and the result is unchanged by timing."""
+    from stereomatch._cstereomatch import AggregationOps
+    H, W, D = 24, 40, 32
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=8, scale="unit")
+    c, l = cuda(O.ssd(left, right, D, 3)), cuda(left)
+    sgm = sm.aggregation.Semiglobal()
+    want = sgm(c, l).clone()
+    AggregationOps.pass_timing(True)
+    try:
+        got = sgm(c, l)
+        passes = AggregationOps.last_pass_ms()
+        assert [d for d, _ in passes] == [0, 1, 2, 3, 4, 5, 6, 7]
+        assert all(t > 0 for _, t in passes)
+        assert torch.equal(got, want)
+        sgm.aggregate_and_reduce(c, l)
+        assert [d for d, _ in AggregationOps.last_pass_ms()] == [0, 1, 2, 3, 4, 5, 7, 6]
+    finally:
+        AggregationOps.pass_timing(False)
+    sgm(c, l)
+    assert AggregationOps.last_pass_ms() == []
+
+
 def test_sgm_reference_arange_recipe(sm):
     """The reference's own equality-test input (tests/test_semiglobalmatch.py:46-47), smaller."""
     H = W = 40
