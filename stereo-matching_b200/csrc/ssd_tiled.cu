@@ -217,11 +217,20 @@ static int run_ssd_tiled(const float *left, const float *right, float *cost, int
   using Cfg = SsdCfg<K, RUNS>;
   const int nx = (W + Cfg::TX - 1) / Cfg::TX;
   const int nd = (D + Cfg::DC - 1) / Cfg::DC;
-  // one CTA per SM: split the rows only when strips x chunks leave SMs idle
-  int ny = num_sms() / (nx * nd);
-  const int max_ny = (H + 63) / 64;  // >= 64 rows per chunk amortises the 2K-1 warm-up rows
-  if (ny > max_ny) ny = max_ny;
-  if (ny < 1) ny = 1;
+  // One CTA per SM, so the launch runs in ceil(CTAs / SMs) waves of equal cost.  Split the rows
+  // into ny chunks (each pays WIN-1 warm-up rows) so that waves x rows-per-chunk is smallest:
+  // D=128 at 1080p is 140 CTAs = one wave (ny = 1); D=192 is 210 CTAs = two waves of full
+  // height, but 420 half-height CTAs = three waves, 1.5 instead of 2 units.
+  const int sms = num_sms();
+  int ny = 1;
+  long best = -1;
+  for (int cand = 1; cand <= 8; ++cand) {
+    const int rows_c = (H + cand - 1) / cand;
+    if (cand > 1 && rows_c < 64) break;  // >= 64 rows per chunk amortises the warm-up rows
+    const long waves = ((long)nx * nd * cand + sms - 1) / sms;
+    const long cost = waves * (rows_c + Cfg::WIN - 1);
+    if (best < 0 || cost < best) { best = cost; ny = cand; }
+  }
   const int rows = (H + ny - 1) / ny;
   ny = (H + rows - 1) / rows;
   if (nd > 65535 || ny > 65535) return fail(STM_EUNSUPPORTED, "ssd: shape too large");
