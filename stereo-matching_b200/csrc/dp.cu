@@ -20,7 +20,7 @@
 
 namespace stm {
 
-template <int NV, int VW>
+template <int NV, int VW, bool DEEP>
 __global__ void __launch_bounds__(128)
 dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
               float *__restrict__ row_final, int32_t *__restrict__ disp, int H, int W, int D) {
@@ -48,7 +48,11 @@ dp_row_kernel(const float *__restrict__ cost, int8_t *__restrict__ path,
   // ---- forward pass.  The cost vectors of the next PF columns stay in flight in registers;
   // every load is unconditional (clamped to the row): a load under a branch is waited for at
   // the join and the pass then runs at one DRAM round trip per column (it did: 1.75 ms).
-  constexpr int PF = (NV * VW <= 4) ? 8 : 4;
+  // Only H warps exist (7 per SM at 1080p), so the bytes each warp keeps in flight decide the
+  // bandwidth: 8 columns (4 KB at D=128) gave 0.51 ms, 24 columns 0.455 ms.  The deep variant
+  // needs ~240 registers (8 warps per SM); the host uses it only while all H rows still fit on
+  // the GPU at once, otherwise the 8-column one (20 warps per SM).
+  constexpr int PF = (NV * VW <= 4) ? (DEEP ? 24 : 8) : 4;
   LaneVec<NV, VW> cbuf[PF];
 #pragma unroll
   for (int u = 0; u < PF; ++u)
@@ -214,8 +218,25 @@ template <int NV, int VW>
 static int run_dp(const float *cost, int8_t *path, float *row_final, int32_t *disp, int H, int W,
                   int D, cudaStream_t stream) {
   const int warps = 4;
-  dp_row_kernel<NV, VW><<<(H + warps - 1) / warps, warps * 32, 0, stream>>>(cost, path, row_final,
-                                                                           disp, H, W, D);
+  const int blocks = (H + warps - 1) / warps;
+  bool deep = false;
+  if (NV * VW <= 4) {
+    static int resident = -1;  // per instantiation
+    if (resident < 0) {
+      int nb = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, dp_row_kernel<NV, VW, true>, warps * 32,
+                                                        0) != cudaSuccess) {
+        cudaGetLastError();
+        nb = 0;
+      }
+      resident = nb * warps * num_sms();
+    }
+    deep = H <= resident;
+  }
+  if (deep)
+    dp_row_kernel<NV, VW, true><<<blocks, warps * 32, 0, stream>>>(cost, path, row_final, disp, H, W, D);
+  else
+    dp_row_kernel<NV, VW, false><<<blocks, warps * 32, 0, stream>>>(cost, path, row_final, disp, H, W, D);
   return check_launch("dp_row_kernel");
 }
 

@@ -260,7 +260,10 @@ def test_dp_cpu_exact_golden(sm, golden, case):
                                           (3, 16, 64, "rand"), (3, 17, 64, "rand"), (3, 18, 64, "rand"),
                                           (6, 700, 128, "rand"), (5, 333, 192, "rand"),
                                           (4, 90, 5, "rand"),    # D smaller than the window
-                                          (3, 120, 256, "rand"), (4, 400, 32, "ties")])
+                                          (3, 120, 256, "rand"), (4, 400, 32, "ties"),
+                                          # more rows than the 24-column-prefetch variant keeps
+                                          # resident: the 8-column variant runs
+                                          (3100, 7, 32, "rand"), (2500, 30, 128, "ties")])
 def test_dp_cuda_mode_vs_oracle(sm, H, W, D, kind):
     if kind == "ssd":
         left, right, _ = synth.random_dot_pair(H, W, D, seed=H + D, scale="raw")
