@@ -1,0 +1,30 @@
+"""String tables and `create_pipeline` for the command-line callers of the path
+(interface of reference stereomatch/cli_common.py:9-52: same keys, same argument order)."""
+from .aggregation import Semiglobal
+from .cost import SSD, Birchfield
+from .disparity_reduce import DynamicProgramming, WinnerTakesAll
+from .pipeline import Pipeline
+
+
+def _no_texture(_max_disparity):
+    # reference cli_common.py:11 maps "ssd-texture" to SSDTexture (CUDA texture objects,
+    # SURVEY.md 8(f) N3); that input path is not provided here, the plain SSD kernel is.
+    raise RuntimeError("cost method 'ssd-texture' is not provided by stereomatch_b200; use 'ssd'")
+
+
+COST_METHODS = {"ssd": SSD, "ssd-texture": _no_texture, "birchfield": Birchfield}
+AGGREGATION_METHODS = {"sgm": Semiglobal}
+DISPARITY_METHODS = {"wta": WinnerTakesAll, "dyn": DynamicProgramming}
+
+
+def create_pipeline(cost_method: str, disp_method: str, aggr_method: str = None,
+                    max_disparity: int = 32) -> Pipeline:
+    """cost_method in COST_METHODS, disp_method in DISPARITY_METHODS, aggr_method in
+    AGGREGATION_METHODS or anything else (None, "") for no aggregation -- as the reference,
+    an unknown aggregation name silently means none; unknown cost/disparity names raise
+    KeyError."""
+    aggregation = AGGREGATION_METHODS.get(aggr_method, None)
+    if aggregation is not None:
+        aggregation = aggregation()
+    return Pipeline(COST_METHODS[cost_method](max_disparity), DISPARITY_METHODS[disp_method](),
+                    aggregation=aggregation)
