@@ -14,19 +14,23 @@
 // integer < 2^24).
 //
 // CTA = one x-strip of TX = RUNS*2K output columns  x  one chunk of 32 disparities,
-// walking down the rows of its y-range.  Two warp roles meet at one barrier per row:
+// walking down the rows of its y-range in HALF-BLOCKS of K rows.  Two warp roles meet at one
+// barrier per half-block (it was one per row: each warp then had ~55 instructions of work
+// between barriers and the kernel ran at 40 % issue utilisation, latency-bound):
 //  * vertical warps: thread = (column c, 4 consecutive d).  Per input row it squares 4
 //    differences (image rows staged in shared memory, conflict-free reads) and advances a
 //    2K-deep van Herk ring held in REGISTERS (fully unrolled, static indices); the
-//    vertical window sum of the row that just completed goes to shared memory as one
-//    float4 (a warp writes 512 contiguous bytes).
-//  * horizontal warps: lane = disparity, warp = a run of 2K output columns.  Reads the
-//    4K-1 vertical sums it needs (128-byte rows, conflict-free), does the prefix/suffix
-//    blocks in registers and streams 2K fully-coalesced 128-byte stores into C.
-// The two roles work on consecutive rows concurrently (double-buffered tile).
-// HBM traffic = the 4 B/pix-disp store of C plus the (L2-resident) images: the kernel is
-// bound by the store stream, shared-memory wavefronts (~4.8 words/output) and FP32 issue
-// in roughly equal parts -- see DESIGN.md.
+//    vertical window sum of each of the K rows goes to the half-block's tile in shared
+//    memory as one float4 (a warp writes 512 contiguous bytes).
+//  * horizontal warps: lane = disparity, warp = a run of 2K output columns.  For each of the
+//    K rows of the PREVIOUS half-block it reads the 4K-1 vertical sums it needs (128-byte
+//    rows, conflict-free), does the prefix/suffix blocks in registers and streams 2K
+//    fully-coalesced 128-byte stores into C.
+// The image rows of the next half-block are requested with cp.async at the start of a
+// half-block and waited for at its end (double-buffered), so their latency is covered by
+// K rows of arithmetic.  HBM traffic = the 4 B/pix-disp store of C plus the images.
+#include <cstdlib>
+
 #include "stm_common.cuh"
 
 namespace stm {
@@ -34,6 +38,7 @@ namespace stm {
 template <int K, int RUNS>
 struct SsdCfg {
   static constexpr int WIN = 2 * K;
+  static constexpr int HALF = K;                // rows per barrier interval
   static constexpr int TX = RUNS * WIN;         // output columns per CTA
   static constexpr int TXH = TX + WIN - 1;      // columns with halo
   static constexpr int DC = 32;                 // disparities per CTA
@@ -41,6 +46,13 @@ struct SsdCfg {
   static constexpr int HWARPS = RUNS;
   static constexpr int THREADS = VTHREADS + HWARPS * 32;
   static constexpr int RROW = TXH + DC - 1;     // staged right-image span
+  static constexpr int RPITCH = RROW + 1;
+  // dynamic shared memory, in floats: vbuf[2][HALF][TXH][DC], lrow[2][HALF][TXH],
+  // rrow[2][HALF][RPITCH]
+  static constexpr int VBUF = 2 * HALF * TXH * DC;
+  static constexpr int LROW = 2 * HALF * TXH;
+  static constexpr int RROWS = 2 * HALF * RPITCH;
+  static constexpr size_t SMEM = (size_t)(VBUF + LROW + RROWS) * sizeof(float);
 };
 
 __device__ __forceinline__ void named_barrier(int threads) {
@@ -52,49 +64,56 @@ __global__ void __launch_bounds__(SsdCfg<K, RUNS>::THREADS, 1)
 ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right,
                  float *__restrict__ cost, int H, int W, int D, int rows_per_chunk) {
   using Cfg = SsdCfg<K, RUNS>;
-  constexpr int WIN = Cfg::WIN, TXH = Cfg::TXH, DC = Cfg::DC;
+  constexpr int WIN = Cfg::WIN, HALF = Cfg::HALF, TXH = Cfg::TXH, DC = Cfg::DC;
 
-  __shared__ __align__(16) float vbuf[2][TXH][DC];
-  __shared__ float lrow[2][TXH];
-  __shared__ float rrow[2][Cfg::RROW + 1];
+  extern __shared__ __align__(16) float smem[];
+  float *vbuf = smem;                       // [(b*HALF + i)*TXH + col][DC]
+  float *lrow = smem + Cfg::VBUF;           // [(b*HALF + i)][TXH]
+  float *rrow = lrow + Cfg::LROW;           // [(b*HALF + i)][RPITCH]
 
   const int tid = threadIdx.x;
   const int x0 = blockIdx.x * Cfg::TX;
   const int d0 = blockIdx.y * DC;
   const int ya = blockIdx.z * rows_per_chunk;
   const int yb = min(H, ya + rows_per_chunk);
-  const int T = (yb - ya) + WIN - 1;   // input rows ya-K .. yb+K-2
-  const int cbase = x0 - K;            // image column of staged column 0
+  const int T = (yb - ya) + WIN - 1;        // input rows ya-K .. yb+K-2
+  const int n_half = (T + HALF - 1) / HALF; // barrier intervals
+  const int cbase = x0 - K;                 // image column of staged column 0
   const int ubase = cbase - d0 - (DC - 1);  // right-image column of rrow[.][0]
 
-  // Cooperative staging of the image rows (zeros outside the image), software-pipelined through
-  // one register: a row is LOADED two iterations before it is used and STORED to shared memory
-  // one iteration before, so no global-load latency sits between two row barriers.  The load is
-  // unconditional (clamped address, value masked when it is stored): a load under a branch
-  // would be waited for at the join.  Threads [0,TXH) stage the left row, the next RROW the
-  // right row; the other vertical threads load a clamped address and store nothing.
+  // Cooperative staging of the image rows of one half-block (zeros outside the image):
+  // cp.async straight from global to shared memory, one group per half-block.  Threads
+  // [0,TXH) stage the left rows, the next RROW threads the right rows; out-of-image pixels
+  // are zero-filled by a source size of 0 (the address is clamped to stay valid).
   static_assert(Cfg::VTHREADS >= TXH + Cfg::RROW, "not enough loader threads");
   const bool st_left = tid < TXH;
   const bool st_any = tid < TXH + Cfg::RROW;
   const int st_col = st_left ? cbase + tid : ubase + (tid - TXH);
   const bool st_col_ok = st_any && st_col >= 0 && st_col < W;
   const float *st_src = (st_left ? left : right) + min(max(st_col, 0), W - 1);
-  float *st_dst0 = st_left ? &lrow[0][tid] : &rrow[0][st_any ? tid - TXH : 0];
-  const int st_stride = st_left ? TXH : Cfg::RROW + 1;  // floats between the two buffers
-  auto fetch = [&](int t) -> float {  // raw value of staged row t (any t)
-    const int r = min(max(ya - K + t, 0), H - 1);
-    return __ldg(st_src + (size_t)r * W);
+  const uint32_t st_dst0 = (uint32_t)__cvta_generic_to_shared(
+      st_left ? lrow + tid : rrow + (st_any ? tid - TXH : 0));
+  const uint32_t st_pitch = (st_left ? TXH : Cfg::RPITCH) * sizeof(float);  // bytes per row slot
+  auto stage_half = [&](int h) {  // request the rows of half-block h (any h >= 0)
+    if (st_any) {
+#pragma unroll
+      for (int i = 0; i < HALF; ++i) {
+        const int r = ya - K + h * HALF + i;
+        const int ok_bytes = (st_col_ok && r >= 0 && r < H) ? 4 : 0;
+        const float *src = st_src + (size_t)min(max(r, 0), H - 1) * W;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(
+                         st_dst0 + (uint32_t)((h & 1) * HALF + i) * st_pitch),
+                     "l"(src), "r"(ok_bytes)
+                     : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  auto put = [&](int t, float raw) {  // store staged row t into buffer t&1
-    const int r = ya - K + t;
-    const bool ok = st_col_ok && r >= 0 && r < H;
-    if (st_any) st_dst0[(t & 1) * st_stride] = ok ? raw : 0.f;
-  };
+  auto staged_landed = [&]() { asm volatile("cp.async.wait_group 0;" ::: "memory"); };
 
-  float staged = 0.f;  // raw value of row t+1 while iteration t runs (vertical role only)
   if (tid < Cfg::VTHREADS) {
-    put(0, fetch(0));
-    staged = fetch(1);
+    stage_half(0);
+    staged_landed();
   }
   __syncthreads();
 
@@ -117,27 +136,37 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
 #pragma unroll
       for (int j = 0; j < 4; ++j) ring[i][j] = 0.f;
 
-    // one input row: jj is a compile-time constant after unrolling (static ring indices)
-    auto row_step = [&](int t, int jj) {
-      const int buf = t & 1;
-      // row t+1 (loaded one iteration ago) goes to shared memory, row t+2 is requested.  Past
-      // the last row both are harmless: the address is clamped and nobody reads the buffer.
-      put(t + 1, staged);
-      staged = fetch(t + 2);
-      float out[4];
+    // one input row of the current block: jj (0..WIN-1) is a compile-time constant after
+    // unrolling, so the ring indices are static and so are the buffer (jj / HALF -- a block is
+    // two half-blocks, hence block-relative half == global half & 1) and the row slot
+    auto row_step = [&](int jj) {
+      const int slot = jj;  // (jj / HALF) * HALF + jj % HALF
       if (active) {
-        const float l = lrow[buf][cl];
+        const float l = lrow[slot * TXH + cl];
+        const float *rr = rrow + slot * Cfg::RPITCH + rbase;
+        float out[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float diff = __fsub_rn(l, rrow[buf][rbase - j]);
+          const float diff = __fsub_rn(l, rr[-j]);
           const float e = valid[j] ? __fmul_rn(diff, diff) : 0.f;
           pre[j] = __fadd_rn(pre[j], e);
           out[j] = (jj < WIN - 1) ? __fadd_rn(ring[(jj + 1) % WIN][j], pre[j]) : pre[j];
           ring[jj][j] = e;
         }
-        *reinterpret_cast<float4 *>(&vbuf[buf][cl][dq * 4]) =
+        *reinterpret_cast<float4 *>(vbuf + ((size_t)slot * TXH + cl) * DC + dq * 4) =
             make_float4(out[0], out[1], out[2], out[3]);
       }
+    };
+    // one half-block: request the next half-block's image rows, sum HALF rows, meet the
+    // horizontal warps.  `b` is 0 or 1 at every call site (constant after inlining).
+    auto half_step = [&](int tb, int b, bool guarded) {
+      stage_half(tb / HALF + b + 1);
+#pragma unroll
+      for (int i = 0; i < HALF; ++i) {
+        const int jj = b * HALF + i;
+        if (!guarded || tb + jj < T) row_step(jj);  // block-uniform
+      }
+      staged_landed();
       named_barrier(Cfg::THREADS);
     };
     // turn the finished block of raw values into suffix sums; restart the prefix
@@ -150,19 +179,15 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
       for (int j = 0; j < 4; ++j) pre[j] = 0.f;
     };
 
-    // Full blocks run without any `t < T` test: a load whose result is merged at the join of
-    // a branch is waited for at that join, which would put the global latency of `fetch`
-    // back between two barriers.  Only the last, partial block is guarded.
     int tb = 0;
     for (; tb + WIN <= T; tb += WIN) {
-#pragma unroll
-      for (int jj = 0; jj < WIN; ++jj) row_step(tb + jj, jj);
+      half_step(tb, 0, false);
+      half_step(tb, 1, false);
       close_block();
     }
-    if (tb < T) {
-#pragma unroll
-      for (int jj = 0; jj < WIN; ++jj)
-        if (tb + jj < T) row_step(tb + jj, jj);  // block-uniform
+    if (tb < T) {  // last, partial block: one barrier per half-block that has a row
+      half_step(tb, 0, true);
+      if (tb + HALF < T) half_step(tb, 1, true);
     }
   } else {
     // ----------------------------- horizontal role -----------------------------------
@@ -172,14 +197,11 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
     const bool d_ok = d < D;
     const int xr = x0 + q * WIN;
     const bool interior = (xr + WIN <= W) && (xr >= d0 + DC - 1) && (d0 + DC <= D);  // warp-uniform
-    auto emit = [&](int t) {
-      // row produced by the vertical warps in iteration t
-      const int y = ya - WIN + 1 + t;
-      if (y < ya) return;
-      const int buf = t & 1;
+    auto emit_row = [&](int slot, int y) {
+      const float *vb = vbuf + ((size_t)slot * TXH + q * WIN) * DC + lane;
       float v[2 * WIN - 1];
 #pragma unroll
-      for (int i = 0; i < 2 * WIN - 1; ++i) v[i] = vbuf[buf][q * WIN + i][lane];
+      for (int i = 0; i < 2 * WIN - 1; ++i) v[i] = vb[i * DC];
       // suffix sums of block A = v[0..WIN), prefix sums of block B = v[WIN..2WIN-1)
 #pragma unroll
       for (int i = WIN - 2; i >= 0; --i) v[i] = __fadd_rn(v[i], v[i + 1]);
@@ -188,8 +210,7 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
       float *orow = cost + ((size_t)y * W + xr) * D + d;
       if (interior) {
         // the whole run lies inside the image, right of every disparity of the chunk, and the
-        // chunk inside [0,D): nothing to test per store (these 4 warps are the serial part of
-        // a row, ~200 instructions each with the tests, ~110 without)
+        // chunk inside [0,D): nothing to test per store
         asm volatile("" : "+l"(orow));  // opaque base: keeps the index arithmetic out of the loop
 #pragma unroll
         for (int j = 0; j < WIN; ++j)  // 32-bit offsets: one IMAD.WIDE per address
@@ -203,11 +224,16 @@ ssd_tiled_kernel(const float *__restrict__ left, const float *__restrict__ right
         }
       }
     };
-    for (int t = 0; t < T; ++t) {
-      if (t > 0) emit(t - 1);
-      named_barrier(Cfg::THREADS);
+    for (int g = 0; g < n_half; ++g) {
+      named_barrier(Cfg::THREADS);  // half-block g sits in tile buffer g & 1
+      const int b = g & 1;
+#pragma unroll
+      for (int i = 0; i < HALF; ++i) {
+        const int t = g * HALF + i;
+        const int y = ya - WIN + 1 + t;  // output row completed by input row t
+        if (t < T && y >= ya) emit_row(b * HALF + i, y);
+      }
     }
-    emit(T - 1);
   }
 }
 
@@ -215,27 +241,33 @@ template <int K, int RUNS>
 static int run_ssd_tiled(const float *left, const float *right, float *cost, int H, int W, int D,
                          cudaStream_t stream) {
   using Cfg = SsdCfg<K, RUNS>;
+  static bool configured = false;
+  if (!configured) {
+    if (cudaFuncSetAttribute(ssd_tiled_kernel<K, RUNS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)Cfg::SMEM) != cudaSuccess) {
+      cudaGetLastError();
+      return 1;  // fall back to the generic kernel
+    }
+    configured = true;
+  }
   const int nx = (W + Cfg::TX - 1) / Cfg::TX;
   const int nd = (D + Cfg::DC - 1) / Cfg::DC;
-  // One CTA per SM, so the launch runs in ceil(CTAs / SMs) waves of equal cost.  Split the rows
-  // into ny chunks (each pays WIN-1 warm-up rows) so that waves x rows-per-chunk is smallest:
-  // D=128 at 1080p is 140 CTAs = one wave (ny = 1); D=192 is 210 CTAs = two waves of full
-  // height, but 420 half-height CTAs = three waves, 1.5 instead of 2 units.
-  const int sms = num_sms();
-  int ny = 1;
-  long best = -1;
-  for (int cand = 1; cand <= 8; ++cand) {
-    const int rows_c = (H + cand - 1) / cand;
-    if (cand > 1 && rows_c < 64) break;  // >= 64 rows per chunk amortises the warm-up rows
-    const long waves = ((long)nx * nd * cand + sms - 1) / sms;
-    const long cost = waves * (rows_c + Cfg::WIN - 1);
-    if (best < 0 || cost < best) { best = cost; ny = cand; }
+  // Rows are split into chunks of ~128 output rows (each chunk pays WIN-1 warm-up rows).  Many
+  // short CTAs beat one full-height CTA per SM by a wide margin -- 1080p D=128: 0.507 ms with
+  // 1 chunk, 0.420 with 2, 0.383 with 4, 0.373 with 8 or 10 (profiles/r01_v18_ssd.txt): the
+  // block scheduler balances them over all SMs, and CTAs working on different image rows
+  // spread the store stream over the DRAM instead of all writing the same ~1 MB at once.
+  int ny = (H + 64) / 128;
+  if (ny < 1) ny = 1;
+  {
+    static const char *force = getenv("STM_DEBUG_SSD_NY");  // developer knob
+    if (force && atoi(force) > 0) ny = atoi(force);
   }
   const int rows = (H + ny - 1) / ny;
   ny = (H + rows - 1) / rows;
   if (nd > 65535 || ny > 65535) return fail(STM_EUNSUPPORTED, "ssd: shape too large");
-  ssd_tiled_kernel<K, RUNS><<<dim3(nx, nd, ny), Cfg::THREADS, 0, stream>>>(left, right, cost, H, W,
-                                                                          D, rows);
+  ssd_tiled_kernel<K, RUNS><<<dim3(nx, nd, ny), Cfg::THREADS, Cfg::SMEM, stream>>>(left, right, cost,
+                                                                                  H, W, D, rows);
   return check_launch("ssd_tiled_kernel");
 }
 
