@@ -257,7 +257,11 @@ static int run_ssd_tiled(const float *left, const float *right, float *cost, int
   // 1 chunk, 0.420 with 2, 0.383 with 4, 0.373 with 8 or 10 (profiles/r01_v18_ssd.txt): the
   // block scheduler balances them over all SMs, and CTAs working on different image rows
   // spread the store stream over the DRAM instead of all writing the same ~1 MB at once.
+  // Small images: at least one CTA per SM as long as a chunk keeps >= 32 rows.
   int ny = (H + 64) / 128;
+  const int fill = (num_sms() + nx * nd - 1) / (nx * nd);
+  if (ny < fill) ny = fill;
+  if (ny > (H + 31) / 32) ny = (H + 31) / 32;
   if (ny < 1) ny = 1;
   {
     static const char *force = getenv("STM_DEBUG_SSD_NY");  // developer knob
