@@ -52,6 +52,11 @@ extern "C" {
                                      the finished sums to the disparity map without writing them
                                      back (4 B/pix-disp less HBM traffic); on return `out` holds
                                      the sum of the first seven directions, not the result. */
+#define STM_SGM_SEQUENTIAL 16u /* always run the eight direction passes one after the other.  Without
+                                  it, landscape / square volumes of at most 48 MB (latency-bound,
+                                  L2-resident: BASELINE.json config 2) run the eight directions
+                                  concurrently into per-direction buffers of the workspace and
+                                  add them in the reference's order -- bit-identical results. */
 
 /* flags of stm_dp_f32 */
 #define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68);
@@ -94,7 +99,7 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
  * equals stm_sgm_f32's result up to fp32 association (a few ulp).  `out` is still written
  * unless STM_SGM_DISPARITY_ONLY is given (what Pipeline.estimate uses: it never hands the
  * aggregated volume to its caller).
- * flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY. */
+ * flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY | STM_SGM_SEQUENTIAL. */
 int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *disparity, int H,
                     int W, int D, float penalty1, float penalty2, unsigned flags, void *workspace,
                     size_t workspace_bytes, void *stream);

@@ -103,7 +103,7 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
   if (rc) return rc;
   STM_REQUIRE(cost && left && out, "sgm: null pointer");
   STM_REQUIRE(cost != out, "sgm: output must not alias the cost volume");
-  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_FUSED_SWEEPS)) == 0, "sgm: unknown flags 0x%x",
+  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_FUSED_SWEEPS | STM_SGM_SEQUENTIAL)) == 0, "sgm: unknown flags 0x%x",
               flags);
   if ((rc = require_device())) return rc;
   return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace,
@@ -117,7 +117,7 @@ int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *d
   if (rc) return rc;
   STM_REQUIRE(cost && left && out && disparity, "sgm_wta: null pointer");
   STM_REQUIRE(cost != out, "sgm_wta: output must not alias the cost volume");
-  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY)) == 0,
+  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY | STM_SGM_SEQUENTIAL)) == 0,
               "sgm_wta: unknown flags 0x%x", flags);
   if ((rc = require_device())) return rc;
   return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace, workspace_bytes,

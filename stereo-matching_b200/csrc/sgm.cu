@@ -609,9 +609,138 @@ static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
   return (size_t)(H < W ? H : W) * dpad * sizeof(float);
 }
 
-size_t sgm_workspace_bytes(int H, int W, int D) {
+// Small, L2-resident volumes (BASELINE.json config 2: 450x375x64 = 43 MB) are not bandwidth-
+// but latency-bound: eight passes of <= 450 dependent steps each, one after the other.  For
+// those the eight directions run CONCURRENTLY on library-owned streams, each into its own
+// buffer, and one kernel then adds the buffers in the reference's order (corner-diagonal
+// replays included), so the result is bit-identical to the sequential passes.  It costs
+// 8 volume-sized buffers of workspace and ~25 % more traffic, hence only below 48 MB.
+constexpr size_t kConcurrentMaxVolumeBytes = (size_t)48 << 20;
+static bool sgm_concurrent_eligible(int H, int W, int D) {
+  return H >= 2 && H <= W && (size_t)H * W * D * sizeof(float) <= kConcurrentMaxVolumeBytes;
+}
+static size_t sgm_base_workspace_bytes(int H, int W, int D) {
   const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_wave_workspace_bytes(H, W, D);
   return a > b ? a : b;
+}
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+size_t sgm_workspace_bytes(int H, int W, int D) {
+  const size_t base = sgm_base_workspace_bytes(H, W, D);
+  if (!sgm_concurrent_eligible(H, W, D)) return base;
+  return align256(base) + (size_t)8 * H * W * D * sizeof(float);
+}
+
+// out = [out +] b0 + b1 + ... + b7, one fp32 addition at a time in the reference's order; the
+// corner up-diagonals (x - y == W - H for direction 5, x + y == H - 1 for direction 7) get
+// their vector `times` more times right after that direction, as the sequential path does.
+template <int VEC>
+__global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict__ bufs,
+                                size_t n_vec, size_t stride, int H, int W, int D, int accumulate,
+                                int times) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_vec) return;
+  const size_t e = i * VEC;           // first element of this thread
+  const size_t pixel = e / D;
+  const int x = (int)(pixel % W), y = (int)(pixel / W);
+  const bool corner5 = times > 0 && x - y == W - H;
+  const bool corner7 = times > 0 && x + y == H - 1;
+  float s[VEC], b[VEC];
+  auto load = [&](const float *p) {
+    if constexpr (VEC == 4) {
+      const float4 t = *reinterpret_cast<const float4 *>(p + e);
+      b[0] = t.x; b[1] = t.y; b[2] = t.z; b[3] = t.w;
+    } else {
+      b[0] = p[e];
+    }
+  };
+  load(bufs);
+  if (accumulate) {
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) s[k] = b[k];
+    load(out);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) s[k] = __fadd_rn(b[k], s[k]);  // out_old + L0
+  } else {
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) s[k] = b[k];
+  }
+  for (int dir = 1; dir < 8; ++dir) {
+    load(bufs + (size_t)dir * stride);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) s[k] = __fadd_rn(s[k], b[k]);
+    if ((dir == 5 && corner5) || (dir == 7 && corner7))
+      for (int r = 0; r < times; ++r)
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) s[k] = __fadd_rn(s[k], b[k]);
+  }
+  if constexpr (VEC == 4) {
+    *reinterpret_cast<float4 *>(out + e) = make_float4(s[0], s[1], s[2], s[3]);
+  } else {
+    out[e] = s[0];
+  }
+}
+
+static cudaStream_t g_aux_stream[7];
+static cudaEvent_t g_fork_event, g_join_event[7];
+static bool g_aux_ready = false;
+static int aux_streams_init() {
+  if (g_aux_ready) return STM_OK;
+  if (cudaEventCreateWithFlags(&g_fork_event, cudaEventDisableTiming) != cudaSuccess)
+    return fail(STM_ECUDA, "sgm: cudaEventCreate failed");
+  for (int i = 0; i < 7; ++i) {
+    if (cudaStreamCreateWithFlags(&g_aux_stream[i], cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&g_join_event[i], cudaEventDisableTiming) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: cudaStreamCreate failed");
+  }
+  g_aux_ready = true;
+  return STM_OK;
+}
+
+int launch_wta(const float *, int32_t *, int, int, int, cudaStream_t);  // wta.cu
+
+template <int NV, int VW>
+static int sgm_concurrent(const float *cost, const float *image, float *out, int H, int W, int D,
+                          float p1, float p2, unsigned flags, float *bufs, cudaStream_t stream,
+                          int32_t *disp) {
+  int rc = aux_streams_init();
+  if (rc) return rc;
+  const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
+  const size_t N = (size_t)H * W * D;
+  if (cudaEventRecord(g_fork_event, stream) != cudaSuccess)
+    return fail(STM_ECUDA, "sgm: cudaEventRecord failed");
+  for (int dir = 0; dir < 8; ++dir) {
+    cudaStream_t s = dir == 0 ? stream : g_aux_stream[dir - 1];
+    float *b = bufs + (size_t)dir * N;
+    if (dir > 0 && cudaStreamWaitEvent(s, g_fork_event, 0) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: cudaStreamWaitEvent failed");
+    // the defective up-diagonals skip a band of a landscape image: those pixels contribute 0
+    if ((dir == 5 || dir == 7) && W > H &&
+        cudaMemsetAsync(b, 0, N * sizeof(float), s) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: cudaMemsetAsync failed");
+    rc = run_direction<NV, VW>(cost, image, b, H, W, D, p1, p2, dir, 0, sgm_num_paths(dir, H, W),
+                               min_limit, 0u, nullptr, -1, s);
+    if (rc) return rc;
+    if (dir > 0) {
+      if (cudaEventRecord(g_join_event[dir - 1], s) != cudaSuccess ||
+          cudaStreamWaitEvent(stream, g_join_event[dir - 1], 0) != cudaSuccess)
+        return fail(STM_ECUDA, "sgm: stream join failed");
+    }
+  }
+  const int times = W - H;  // extra runs of the corner diagonals (0 on square images)
+  const int accumulate = (flags & STM_SGM_OVERWRITE) ? 0 : 1;
+  if (D % 4 == 0) {
+    const size_t n_vec = N / 4;
+    sgm_sum8_kernel<4><<<(unsigned)((n_vec + 255) / 256), 256, 0, stream>>>(out, bufs, n_vec, N, H, W,
+                                                                          D, accumulate, times);
+  } else {
+    sgm_sum8_kernel<1><<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(out, bufs, N, N, H, W, D,
+                                                                      accumulate, times);
+  }
+  rc = check_launch("sgm_sum8_kernel");
+  if (rc) return rc;
+  if (disp) return launch_wta(out, disp, H, W, D, stream);
+  return STM_OK;
 }
 
 // Developer hook (tools/sgm_plan.py): resident-warp capacity of the D=128 variants and the
@@ -642,6 +771,23 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   }
   const LaneMap m = pick_lane_map(D);
   float *ws = static_cast<float *>(workspace);
+  {
+    static const char *off = getenv("STM_DEBUG_SGM_CONCURRENT");  // developer knob: "0" disables
+    // (per-pass timing measures the sequential passes, so it selects them)
+    if (sgm_concurrent_eligible(H, W, D) && !(flags & STM_SGM_SEQUENTIAL) && !g_pass_timing &&
+        !(off && off[0] == '0')) {
+      float *bufs = reinterpret_cast<float *>(static_cast<char *>(workspace) +
+                                              align256(sgm_base_workspace_bytes(H, W, D)));
+#define STM_SGM_CC(NV_, VW_)          \
+  if (m.NV == NV_ && m.VW == VW_)     \
+    return sgm_concurrent<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, bufs, stream, disp);
+      STM_SGM_CC(1, 4) STM_SGM_CC(2, 4) STM_SGM_CC(3, 4) STM_SGM_CC(4, 4)
+      STM_SGM_CC(1, 2) STM_SGM_CC(3, 2) STM_SGM_CC(5, 2) STM_SGM_CC(7, 2)
+      STM_SGM_CC(1, 1) STM_SGM_CC(2, 1) STM_SGM_CC(3, 1) STM_SGM_CC(4, 1)
+      STM_SGM_CC(5, 1) STM_SGM_CC(6, 1) STM_SGM_CC(7, 1) STM_SGM_CC(8, 1)
+#undef STM_SGM_CC
+    }
+  }
 #define STM_SGM_CASE(NV_, VW_)                                                            \
   if (m.NV == NV_ && m.VW == VW_)                                                         \
     return H > W ? sgm_by_direction_portrait<NV_, VW_>(cost, image, out, H, W, D, p1, p2,  \

@@ -22,6 +22,7 @@ STM_SGM_MIN_ALL_D = 1
 STM_SGM_OVERWRITE = 2
 STM_SGM_FUSED_SWEEPS = 4
 STM_SGM_DISPARITY_ONLY = 8
+STM_SGM_SEQUENTIAL = 16
 STM_DP_CPU_EXACT = 1
 
 if not _LIB_PATH.exists():

@@ -5,7 +5,7 @@ import torch
 
 from ._common import empty_tensor
 from ._cstereomatch import (STM_SGM_MIN_ALL_D, STM_SGM_OVERWRITE, STM_SGM_FUSED_SWEEPS,
-                             STM_SGM_DISPARITY_ONLY)
+                             STM_SGM_DISPARITY_ONLY, STM_SGM_SEQUENTIAL)
 from ._cstereomatch import AggregationOps as _AggregationOps
 
 
@@ -21,15 +21,20 @@ class Semiglobal:
     The default runs one kernel per direction and adds the eight directions into the output
     in the reference's order.  fused_sweeps=True (experimental) computes them in two raster
     sweeps: a quarter of the HBM traffic and the same values within a few ulp, but it is
-    latency-bound and currently about 5x slower.
+    latency-bound and currently about 5x slower.  concurrent_directions=True (default) lets
+    small landscape / square volumes (<= 48 MB, latency-bound) run the eight directions at
+    the same time into per-direction buffers that are then added in the reference's order --
+    bit-identical to the sequential passes, which concurrent_directions=False forces.
     """
 
     def __init__(self, penalty1: float = 0.1, penalty2: float = 0.2, *,
-                 min_over_all_d: bool = False, fused_sweeps: bool = False):
+                 min_over_all_d: bool = False, fused_sweeps: bool = False,
+                 concurrent_directions: bool = True):
         self.penalty1 = penalty1
         self.penalty2 = penalty2
         self.min_over_all_d = min_over_all_d
         self.fused_sweeps = fused_sweeps
+        self.concurrent_directions = concurrent_directions
 
     def __call__(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
                  sga_volume: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -39,6 +44,8 @@ class Semiglobal:
         sga_volume = empty_tensor(*cost_volume.size(), dtype=cost_volume.dtype,
                                   device=cost_volume.device, reuse_tensor=sga_volume)
         flags = STM_SGM_OVERWRITE | (STM_SGM_MIN_ALL_D if self.min_over_all_d else 0)
+        if not self.concurrent_directions:
+            flags |= STM_SGM_SEQUENTIAL
         if self.fused_sweeps:
             flags |= STM_SGM_FUSED_SWEEPS
         _AggregationOps.run_semiglobal(cost_volume, left_image, self.penalty1, self.penalty2,
@@ -62,6 +69,8 @@ class Semiglobal:
         flags = STM_SGM_OVERWRITE | (STM_SGM_MIN_ALL_D if self.min_over_all_d else 0)
         if not keep_volume:
             flags |= STM_SGM_DISPARITY_ONLY
+        if not self.concurrent_directions:
+            flags |= STM_SGM_SEQUENTIAL
         _AggregationOps.run_semiglobal_wta(cost_volume, left_image, self.penalty1, self.penalty2,
                                            sga_volume, disparity_img, flags)
         return sga_volume, disparity_img

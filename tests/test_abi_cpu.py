@@ -50,6 +50,12 @@ def test_workspace_query_is_pure():
     assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == expect(1080, 1920, 128)
     assert lib.stm_sgm_workspace_bytes(30, 18, 16) == expect(30, 18, 32)  # D=16 pads to 32 lanes
     assert lib.stm_sgm_workspace_bytes(0, 0, 0) == 0
+    # landscape / square volumes up to 48 MB also get one buffer per direction (csrc/sgm.cu,
+    # concurrent directions), after the base workspace rounded up to 256 bytes
+    a256 = lambda n: (n + 255) // 256 * 256
+    for H, W, D, dpad in ((375, 450, 64, 64), (20, 30, 32, 32), (64, 64, 128, 128)):
+        assert lib.stm_sgm_workspace_bytes(H, W, D) == a256(expect(H, W, dpad)) + 8 * H * W * D * 4
+    assert lib.stm_sgm_workspace_bytes(480, 640, 128) == expect(480, 640, 128)   # 157 MB: sequential
 
 
 def test_python_api_surface_matches_reference():

@@ -122,14 +122,15 @@ def test_sgm_golden(sm, golden, case):
     (35, 13, 96, "unit", 0.3, 1.0, True), (11, 29, 20, "raw", 5.0, 9.0, False),
     (1, 9, 32, "unit", 0.1, 0.2, False), (9, 1, 32, "unit", 0.1, 0.2, False),
 ])
-@pytest.mark.parametrize("fused_sweeps", [False, True])
-def test_sgm_vs_oracle(sm, H, W, D, scale, p1, p2, all_d, fused_sweeps):
-    """Both SGM modes: one kernel per direction (default) and the fused raster sweeps."""
+@pytest.mark.parametrize("mode", ["default", "sequential", "fused_sweeps"])
+def test_sgm_vs_oracle(sm, H, W, D, scale, p1, p2, all_d, mode):
+    """All SGM modes: one kernel per direction -- concurrently for these small volumes
+    (default) or one after the other -- and the fused raster sweeps."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 7 + W, scale=scale)
     cost = O.ssd(left, right, D, 3)
     want = O.sgm(cost, left, p1, p2, min_over_all_d=all_d)
-    got = sm.aggregation.Semiglobal(p1, p2, min_over_all_d=all_d,
-                                    fused_sweeps=fused_sweeps)(cuda(cost), cuda(left))
+    got = sm.aggregation.Semiglobal(p1, p2, min_over_all_d=all_d, fused_sweeps=mode == "fused_sweeps",
+                                    concurrent_directions=mode != "sequential")(cuda(cost), cuda(left))
     assert_volume_close(got, want)
 
 
@@ -143,12 +144,12 @@ def test_sgm_horizontal_bulk_copy_kernel_tiles(sm, H, W, D):
     cost = synth.random_volume(H, W, D, seed=D + W, hi=3.0)
     want = O.sgm(cost, left, 0.1, 0.2)
     c, l = cuda(cost), cuda(left)
-    got = sm.aggregation.Semiglobal()(c, l)
+    got = sm.aggregation.Semiglobal(concurrent_directions=False)(c, l)   # these kernels run
     assert_volume_close(got, want)
     # the raw op accumulates: direction 0 then runs the read-modify-write variant too
-    from stereomatch._cstereomatch import AggregationOps
+    from stereomatch._cstereomatch import AggregationOps, STM_SGM_SEQUENTIAL
     acc = torch.zeros_like(got)
-    AggregationOps.run_semiglobal(c, l, 0.1, 0.2, acc)
+    AggregationOps.run_semiglobal(c, l, 0.1, 0.2, acc, STM_SGM_SEQUENTIAL)
     assert torch.equal(acc, got)            # 0 + L is exact, the rest is the same sequence
 
 
@@ -181,6 +182,37 @@ def test_sgm_accumulates_like_the_reference(sm):
     AggregationOps.run_semiglobal(cuda(cost), cuda(left), 0.1, 0.2, out)
     want = O.sgm(cost, left, 0.1, 0.2, out=base.copy())
     assert_volume_close(out, want)
+
+
+@pytest.mark.parametrize("H,W,D", [(20, 33, 32), (24, 24, 64), (17, 60, 128), (13, 35, 192), (11, 29, 20)])
+def test_sgm_concurrent_directions_equal_the_sequential_passes(sm, H, W, D):
+    """Small landscape / square volumes run the eight directions concurrently into separate
+    buffers and add them in the reference's order: bit-identical to the sequential passes
+    (STM_SGM_SEQUENTIAL), for the plain call and the accumulating raw op; with the folded
+    winner-takes-all the volume is in reference order (the sequential fold swaps 6 and 7)."""
+    from stereomatch._cstereomatch import AggregationOps, STM_SGM_SEQUENTIAL
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 3 + W, scale="unit")
+    c, l = cuda(O.ssd(left, right, D, 3)), cuda(left)
+    conc_op = sm.aggregation.Semiglobal()
+    seq_op = sm.aggregation.Semiglobal(concurrent_directions=False)
+    base = cuda(synth.random_volume(H, W, D, seed=4, hi=2.0))
+    conc, seq = conc_op(c, l).clone(), seq_op(c, l).clone()
+    assert torch.equal(conc, seq)
+    conc_acc, seq_acc = base.clone(), base.clone()
+    AggregationOps.run_semiglobal(c, l, 0.1, 0.2, conc_acc)
+    AggregationOps.run_semiglobal(c, l, 0.1, 0.2, seq_acc, STM_SGM_SEQUENTIAL)
+    assert torch.equal(conc_acc, seq_acc)
+    assert_volume_close(conc, O.sgm(O.ssd(left, right, D, 3), left, 0.1, 0.2))
+    vol_c, disp_c = conc_op.aggregate_and_reduce(c, l)
+    assert torch.equal(vol_c, seq)
+    assert torch.equal(disp_c, sm.disparity_reduce.WinnerTakesAll()(vol_c))
+    # per-pass timing measures sequential passes, so it selects them
+    AggregationOps.pass_timing(True)
+    try:
+        assert torch.equal(conc_op(c, l), seq)
+        assert len(AggregationOps.last_pass_ms()) == 8
+    finally:
+        AggregationOps.pass_timing(False)
 
 
 def test_sgm_pass_timing_api(sm):
@@ -320,13 +352,15 @@ def test_pipeline_host_entry_point(sm):
                                           (17, 60, 128, "ssd"), (13, 35, 192, "ssd"), (11, 29, 20, "ssd"),
                                           (9, 33, 32, "ties"), (1, 9, 32, "ssd"), (9, 1, 32, "ssd"),
                                           (70, 150, 128, "ssd")])
-def test_sgm_with_wta_folded_into_the_last_pass(sm, H, W, D, kind):
+@pytest.mark.parametrize("concurrent", [False, True])
+def test_sgm_with_wta_folded_into_the_last_pass(sm, H, W, D, kind, concurrent):
     """stm_sgm_wta_f32: the disparity map is EXACTLY WinnerTakesAll of the volume it returns
-    (landscape, portrait, square, ties, odd D), and that volume is the oracle's SGM to 1e-4."""
+    (landscape, portrait, square, ties, odd D), and that volume is the oracle's SGM to 1e-4 --
+    with the argmin folded into the last sequential pass, and with concurrent directions."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 5 + W, scale="unit")
     cost = O.ssd(left, right, D, 3) if kind == "ssd" else synth.tie_heavy_volume(H, W, D, seed=D)
     c, l = cuda(cost), cuda(left)
-    sgm = sm.aggregation.Semiglobal()
+    sgm = sm.aggregation.Semiglobal(concurrent_directions=concurrent)
     vol, disp = sgm.aggregate_and_reduce(c, l)
     assert disp.dtype == torch.int32 and tuple(disp.shape) == (H, W)
     assert_volume_close(vol, O.sgm(cost, left, 0.1, 0.2))
@@ -339,10 +373,12 @@ def test_sgm_with_wta_folded_into_the_last_pass(sm, H, W, D, kind):
     want = disp.clone()
     scratch, disp3 = sgm.aggregate_and_reduce(c, l, keep_volume=False)
     assert torch.equal(disp3, want)
-    assert not torch.equal(scratch, vol)      # the volume really was left unfinished
+    if not concurrent:
+        assert not torch.equal(scratch, vol)  # sequential fold: the volume really was left unfinished
 
 
-def test_sgm_wta_fold_argmin_rule_with_nan_and_inf(sm):
+@pytest.mark.parametrize("concurrent", [False, True])
+def test_sgm_wta_fold_argmin_rule_with_nan_and_inf(sm, concurrent):
     """Pixels whose whole cost vector is +inf turn into NaN sums (inf - inf) that spread along
     the paths: the folded argmin must follow the same rule as the WTA kernel and the oracle
     (first minimum, NaN never wins, NaN at d = 0 -> 0, all-inf -> 0) on the SAME volume."""
@@ -353,7 +389,8 @@ def test_sgm_wta_fold_argmin_rule_with_nan_and_inf(sm):
     vol[5, 6, 0] = np.inf
     vol[:, 0, 1:] = np.inf          # like d > x
     img = synth.random_volume(H, W, 1, seed=6, hi=255.0)[:, :, 0]
-    agg, disp = sm.aggregation.Semiglobal().aggregate_and_reduce(cuda(vol), cuda(img))
+    agg, disp = sm.aggregation.Semiglobal(concurrent_directions=concurrent).aggregate_and_reduce(
+        cuda(vol), cuda(img))
     a = agg.cpu().numpy()
     assert np.isnan(a).any() and np.isinf(a).any()      # the case is what it claims to be
     assert np.array_equal(disp.cpu().numpy(), O.wta(a))
