@@ -85,7 +85,11 @@ int stm_birchfield_f32(const float *left, const float *right, float *cost, int H
  * (reference src/aggregation.cpp:6 -> AggregationOps::RunSemiglobal, src/semiglobal.cpp:167-197).
  * Aggregates over the reference path set (8 directions, including its stored-end quirk)
  * and ACCUMULATES into `out` unless STM_SGM_OVERWRITE.  `workspace` must hold
- * stm_sgm_workspace_bytes(H, W, D) bytes of device memory (may be NULL if that is 0). */
+ * stm_sgm_workspace_bytes(H, W, D) bytes of device memory (may be NULL if that is 0): one
+ * path's worth of vectors for the corner-diagonal replay, the rings of the experimental fused
+ * sweeps and, for landscape / square volumes of at most 48 MB, eight volume-sized buffers (those
+ * shapes run the eight directions concurrently on library-owned streams that are forked from and
+ * joined to `stream`; see STM_SGM_SEQUENTIAL).  The query is a pure function of the shape. */
 size_t stm_sgm_workspace_bytes(int H, int W, int D);
 int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, int D,
                 float penalty1, float penalty2, unsigned flags, void *workspace,

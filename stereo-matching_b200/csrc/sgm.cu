@@ -681,19 +681,31 @@ __global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict
   }
 }
 
-static cudaStream_t g_aux_stream[7];
-static cudaEvent_t g_fork_event, g_join_event[7];
-static bool g_aux_ready = false;
-static int aux_streams_init() {
-  if (g_aux_ready) return STM_OK;
-  if (cudaEventCreateWithFlags(&g_fork_event, cudaEventDisableTiming) != cudaSuccess)
-    return fail(STM_ECUDA, "sgm: cudaEventCreate failed");
-  for (int i = 0; i < 7; ++i) {
-    if (cudaStreamCreateWithFlags(&g_aux_stream[i], cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&g_join_event[i], cudaEventDisableTiming) != cudaSuccess)
-      return fail(STM_ECUDA, "sgm: cudaStreamCreate failed");
+// Helper streams and events, one set per device ordinal (a process normally drives one GPU,
+// but streams and events belong to the device that was current when they were created).
+constexpr int kMaxDevices = 16;
+struct AuxStreams {
+  cudaStream_t stream[7];
+  cudaEvent_t fork, join[7];
+  bool ready = false;
+};
+static AuxStreams g_aux[kMaxDevices];
+static int aux_streams(AuxStreams **out) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices)
+    return fail(STM_ECUDA, "sgm: unsupported device ordinal");
+  AuxStreams &a = g_aux[dev];
+  if (!a.ready) {
+    if (cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: cudaEventCreate failed");
+    for (int i = 0; i < 7; ++i) {
+      if (cudaStreamCreateWithFlags(&a.stream[i], cudaStreamNonBlocking) != cudaSuccess ||
+          cudaEventCreateWithFlags(&a.join[i], cudaEventDisableTiming) != cudaSuccess)
+        return fail(STM_ECUDA, "sgm: cudaStreamCreate failed");
+    }
+    a.ready = true;
   }
-  g_aux_ready = true;
+  *out = &a;
   return STM_OK;
 }
 
@@ -703,16 +715,17 @@ template <int NV, int VW>
 static int sgm_concurrent(const float *cost, const float *image, float *out, int H, int W, int D,
                           float p1, float p2, unsigned flags, float *bufs, cudaStream_t stream,
                           int32_t *disp) {
-  int rc = aux_streams_init();
+  AuxStreams *aux = nullptr;
+  int rc = aux_streams(&aux);
   if (rc) return rc;
   const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
   const size_t N = (size_t)H * W * D;
-  if (cudaEventRecord(g_fork_event, stream) != cudaSuccess)
+  if (cudaEventRecord(aux->fork, stream) != cudaSuccess)
     return fail(STM_ECUDA, "sgm: cudaEventRecord failed");
   for (int dir = 0; dir < 8; ++dir) {
-    cudaStream_t s = dir == 0 ? stream : g_aux_stream[dir - 1];
+    cudaStream_t s = dir == 0 ? stream : aux->stream[dir - 1];
     float *b = bufs + (size_t)dir * N;
-    if (dir > 0 && cudaStreamWaitEvent(s, g_fork_event, 0) != cudaSuccess)
+    if (dir > 0 && cudaStreamWaitEvent(s, aux->fork, 0) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: cudaStreamWaitEvent failed");
     // the defective up-diagonals skip a band of a landscape image: those pixels contribute 0
     if ((dir == 5 || dir == 7) && W > H &&
@@ -722,8 +735,8 @@ static int sgm_concurrent(const float *cost, const float *image, float *out, int
                                min_limit, 0u, nullptr, -1, s);
     if (rc) return rc;
     if (dir > 0) {
-      if (cudaEventRecord(g_join_event[dir - 1], s) != cudaSuccess ||
-          cudaStreamWaitEvent(stream, g_join_event[dir - 1], 0) != cudaSuccess)
+      if (cudaEventRecord(aux->join[dir - 1], s) != cudaSuccess ||
+          cudaStreamWaitEvent(stream, aux->join[dir - 1], 0) != cudaSuccess)
         return fail(STM_ECUDA, "sgm: stream join failed");
     }
   }
