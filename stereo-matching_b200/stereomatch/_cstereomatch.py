@@ -95,10 +95,14 @@ _workspaces = {}
 
 
 def _sgm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    ws = _workspaces.get(device)
+    # one workspace per (device, stream): two pipelines aggregating on different streams at the
+    # same time (stereomatch.streaming) must not share the corner-diagonal store
+    with torch.cuda.device(device):
+        key = (device, _stream())
+    ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=device)
-        _workspaces[device] = ws
+        _workspaces[key] = ws
     return ws
 
 

@@ -415,16 +415,48 @@ def test_pipeline_fused_and_unfused_agree(sm):
     assert float((b.cpu().numpy() != want).mean()) <= 1e-3
 
 
-def test_host_frame_streamer_matches_per_frame_estimate(sm):
+def _ssd_sgm_wta(sm, D):
+    return sm.Pipeline(sm.cost.SSD(D), sm.disparity_reduce.WinnerTakesAll(), sm.aggregation.Semiglobal())
+
+
+@pytest.mark.parametrize("H,W,D,n_pipes", [(40, 96, 32, 1), (40, 96, 32, 2), (40, 96, 32, 3),
+                                            (300, 400, 128, 2)])   # 61 MB: sequential SGM passes
+def test_batch_estimator_matches_per_frame_estimate(sm, H, W, D, n_pipes):
+    """Frames round-robin over several Pipelines on their own streams return exactly what one
+    Pipeline returns frame by frame (no shared workspace, no shared result buffer), with and
+    without caller-provided outputs, and when called twice."""
+    n_frames = 5
+    frames = [synth.random_dot_pair(H, W, D, seed=700 + f, scale="unit")[:2] for f in range(n_frames)]
+    dev = [(cuda(l), cuda(r)) for l, r in frames]
+    ref_pipe = _ssd_sgm_wta(sm, D)
+    want = [ref_pipe.estimate(l, r).clone() for l, r in dev]
+    batch = sm.streaming.BatchEstimator([_ssd_sgm_wta(sm, D) for _ in range(n_pipes)], "cuda")
+    got = batch.estimate_batch(dev)
+    torch.cuda.current_stream().synchronize()
+    assert len(got) == n_frames and all(torch.equal(g, w) for g, w in zip(got, want))
+    outs = [torch.full((H, W), -1, dtype=torch.int32, device="cuda") for _ in frames]
+    for _ in range(2):
+        back = batch.estimate_batch(dev, outs)
+        torch.cuda.current_stream().synchronize()
+        assert all(b.data_ptr() == o.data_ptr() for b, o in zip(back, outs))
+        assert all(torch.equal(o, w) for o, w in zip(outs, want))
+    with pytest.raises(ValueError, match="distinct"):
+        p = _ssd_sgm_wta(sm, D)
+        sm.streaming.BatchEstimator([p, p])
+
+
+@pytest.mark.parametrize("extra", [0, 1, 2])
+def test_host_frame_streamer_matches_per_frame_estimate(sm, extra):
     """Overlapped upload / compute / download returns exactly what Pipeline.estimate returns,
-    for more frames than device buffers and when called twice."""
+    for more frames than device buffers, with one or several compute streams, called twice."""
     H, W, D = 40, 96, 32
-    frames = [synth.random_dot_pair(H, W, D, seed=400 + f, scale="unit")[:2] for f in range(5)]
-    pipe = sm.Pipeline(sm.cost.SSD(D), sm.disparity_reduce.WinnerTakesAll(), sm.aggregation.Semiglobal())
+    frames = [synth.random_dot_pair(H, W, D, seed=400 + f, scale="unit")[:2] for f in range(7)]
+    pipe = _ssd_sgm_wta(sm, D)
     want = [pipe.estimate(cuda(l), cuda(r)).cpu().clone() for l, r in frames]
     pinned = [(torch.from_numpy(l).pin_memory(), torch.from_numpy(r).pin_memory()) for l, r in frames]
     outs = [torch.full((H, W), -1, dtype=torch.int32).pin_memory() for _ in frames]
-    streamer = sm.streaming.HostFrameStreamer(pipe, "cuda")
+    streamer = sm.streaming.HostFrameStreamer(pipe, "cuda",
+                                              extra_pipelines=[_ssd_sgm_wta(sm, D) for _ in range(extra)])
     for _ in range(2):
         for o in outs:
             o.fill_(-1)
