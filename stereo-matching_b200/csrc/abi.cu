@@ -117,7 +117,8 @@ int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *d
   if (rc) return rc;
   STM_REQUIRE(cost && left && out && disparity, "sgm_wta: null pointer");
   STM_REQUIRE(cost != out, "sgm_wta: output must not alias the cost volume");
-  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY | STM_SGM_SEQUENTIAL)) == 0,
+  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY | STM_SGM_SEQUENTIAL |
+                         STM_SGM_FUSED_SWEEPS)) == 0,
               "sgm_wta: unknown flags 0x%x", flags);
   if ((rc = require_device())) return rc;
   return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace, workspace_bytes,
@@ -182,7 +183,7 @@ int stm_pipeline_host_f32(const float *left, const float *right, int32_t *dispar
   if (use_sgm) {
     const size_t wsb = sgm_workspace_bytes(H, W, D);
     if ((rc = s.ensure(kS, N * 4)) || (rc = s.ensure(kWs, wsb ? wsb : 16))) return rc;
-    const bool fuse_wta = reducer == 0 && !(sgm_flags & STM_SGM_FUSED_SWEEPS);
+    const bool fuse_wta = reducer == 0;
     rc = launch_sgm(dc, dl, (float *)s.ptr[kS], H, W, D, penalty1, penalty2,
                     sgm_flags | STM_SGM_OVERWRITE | (fuse_wta ? STM_SGM_DISPARITY_ONLY : 0u),
                     s.ptr[kWs], s.cap[kWs], st, fuse_wta ? (int32_t *)s.ptr[kDisp] : nullptr);

@@ -142,4 +142,34 @@ __device__ __forceinline__ float sgm_p2_adjusted(float p1, float p2, float inten
   return (p1 < q) ? q : p1;
 }
 
+// Winner-takes-all of one pixel's vector held across the warp, with the rule of wta.cu /
+// reference src/winners_take_all.cu:21-40: first (lowest-d) minimum, all-inf -> 0, NaN never
+// wins, NaN at d = 0 -> 0.  Used when the LAST aggregation pass also emits the disparity map.
+template <int NV, int VW>
+__device__ __forceinline__ void lv_argmin_store(const LaneVec<NV, VW> &o, int lane, int D,
+                                                int32_t *dst) {
+  // two warp reductions instead of a (value, index) shuffle butterfly, which costs this
+  // latency-sensitive kernel as much as the separate WTA pass it replaces (measured):
+  // m = minimum over the non-NaN entries (redux.sync.min.f32 returns the non-NaN operand),
+  // then the lowest d whose entry equals m (integer redux).  All-inf: m = inf matches d = 0.
+  float m = CUDART_INF_F;
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int j = 0; j < VW; ++j)
+      if (lv_d<NV, VW>(lane, k, j) < D) m = fminf(m, o.v[k][j]);
+  m = warp_min_f32(m);
+  unsigned idx = 0x7fffffffu;
+#pragma unroll
+  for (int k = NV - 1; k >= 0; --k)
+#pragma unroll
+    for (int j = VW - 1; j >= 0; --j) {
+      const int d = lv_d<NV, VW>(lane, k, j);
+      if (d < D && o.v[k][j] == m) idx = (unsigned)d;  // descending d: the lowest one sticks
+    }
+  idx = __reduce_min_sync(FULL, idx);
+  const bool nan0 = __shfl_sync(FULL, (o.v[0][0] != o.v[0][0]) ? 1 : 0, 0) != 0;
+  if (lane == 0) *dst = (nan0 || idx == 0x7fffffffu) ? 0 : (int)idx;
+}
+
 }  // namespace stm

@@ -28,36 +28,6 @@ enum : unsigned { kSgmAccumulate = 1u, kSgmStoreL = 2u, kSgmNoOutput = 4u, kSgmE
                   kSgmSkipVolumeStore = 16u /* with kSgmEmitWta: the sum is reduced, not written */,
                   kSgmReverseOrder = 32u /* warps take the paths of the direction last to first */ };
 
-// Winner-takes-all of one pixel's vector held across the warp, with the rule of wta.cu /
-// reference src/winners_take_all.cu:21-40: first (lowest-d) minimum, all-inf -> 0, NaN never
-// wins, NaN at d = 0 -> 0.  Used when the LAST aggregation pass also emits the disparity map.
-template <int NV, int VW>
-__device__ __forceinline__ void lv_argmin_store(const LaneVec<NV, VW> &o, int lane, int D,
-                                                int32_t *dst) {
-  // two warp reductions instead of a (value, index) shuffle butterfly, which costs this
-  // latency-sensitive kernel as much as the separate WTA pass it replaces (measured):
-  // m = minimum over the non-NaN entries (redux.sync.min.f32 returns the non-NaN operand),
-  // then the lowest d whose entry equals m (integer redux).  All-inf: m = inf matches d = 0.
-  float m = CUDART_INF_F;
-#pragma unroll
-  for (int k = 0; k < NV; ++k)
-#pragma unroll
-    for (int j = 0; j < VW; ++j)
-      if (lv_d<NV, VW>(lane, k, j) < D) m = fminf(m, o.v[k][j]);
-  m = warp_min_f32(m);
-  unsigned idx = 0x7fffffffu;
-#pragma unroll
-  for (int k = NV - 1; k >= 0; --k)
-#pragma unroll
-    for (int j = VW - 1; j >= 0; --j) {
-      const int d = lv_d<NV, VW>(lane, k, j);
-      if (d < D && o.v[k][j] == m) idx = (unsigned)d;  // descending d: the lowest one sticks
-    }
-  idx = __reduce_min_sync(FULL, idx);
-  const bool nan0 = __shfl_sync(FULL, (o.v[0][0] != o.v[0][0]) ? 1 : 0, 0) != 0;
-  if (lane == 0) *dst = (nan0 || idx == 0x7fffffffu) ? 0 : (int)idx;
-}
-
 // Prefetch depth per lane-vector size.  PFSEL 0 = default; 1 = deep (twice as many pixels in
 // flight, for directions with so few paths that they all fit on the GPU anyway); 2 = shallow:
 // at most 128 registers, so 4 instead of 3 CTAs (16 instead of 12 warps) are resident per SM
@@ -598,10 +568,47 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
   return STM_OK;
 }
 
-// sgm_wave.cu
-size_t sgm_wave_workspace_bytes(int H, int W, int D);
-int launch_sgm_wave(const float *, const float *, float *, int, int, int, float, float, unsigned,
-                    void *, size_t, cudaStream_t);
+// sgm_vsweep.cu
+size_t sgm_vsweep_workspace_bytes(int H, int W, int D);
+bool sgm_vsweep_can_run(int H, int W, int D);
+int launch_sgm_vsweep(const float *, const float *, float *, int32_t *, int, int, int, float, float,
+                      int, int, bool, void *, size_t, cudaStream_t);
+
+// STM_SGM_FUSED_SWEEPS: the two horizontal directions as passes of their own, then the six
+// directions with a vertical component as two fused sweeps (sgm_vsweep.cu): four passes over
+// the volumes instead of eight.  The last sweep can emit the disparity map.  Returns 1 when
+// the shape is not handled by the sweeps (nothing has been launched then).
+template <int NV, int VW>
+static int sgm_fused(const float *cost, const float *image, float *out, int H, int W, int D,
+                     float p1, float p2, unsigned flags, void *ws, size_t ws_bytes,
+                     cudaStream_t stream, int32_t *disp) {
+  const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
+  if (ws == nullptr || ws_bytes < sgm_vsweep_workspace_bytes(H, W, D) || !sgm_vsweep_can_run(H, W, D))
+    return 1;
+  if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) |
+       reinterpret_cast<uintptr_t>(ws)) & 15)
+    return 1;
+  int rc;
+  for (int dir = 0; dir < 2; ++dir) {
+    pass_mark(dir, dir, stream);
+    const unsigned mode = (dir == 0 && (flags & STM_SGM_OVERWRITE)) ? 0u : kSgmAccumulate;
+    rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, dir, 0, H, min_limit, mode,
+                               nullptr, -1, stream);
+    if (rc) return rc;
+  }
+  pass_mark(2, 2, stream);
+  rc = launch_sgm_vsweep(cost, image, out, nullptr, H, W, D, p1, p2, min_limit, 0, true, ws,
+                         ws_bytes, stream);
+  if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
+  if (rc) return rc;
+  pass_mark(3, 3, stream);
+  rc = launch_sgm_vsweep(cost, image, out, disp, H, W, D, p1, p2, min_limit, 1,
+                         !(disp && (flags & STM_SGM_DISPARITY_ONLY)), ws, ws_bytes, stream);
+  if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
+  if (rc) return rc;
+  pass_mark(4, -1, stream);
+  return STM_OK;
+}
 
 static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
   const LaneMap m = pick_lane_map(D);
@@ -620,7 +627,7 @@ static bool sgm_concurrent_eligible(int H, int W, int D) {
   return H >= 2 && H <= W && (size_t)H * W * D * sizeof(float) <= kConcurrentMaxVolumeBytes;
 }
 static size_t sgm_base_workspace_bytes(int H, int W, int D) {
-  const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_wave_workspace_bytes(H, W, D);
+  const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_vsweep_workspace_bytes(H, W, D);
   return a > b ? a : b;
 }
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -776,13 +783,17 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   if (workspace_bytes < sgm_workspace_bytes(H, W, D) || (workspace == nullptr && H != W))
     return fail(STM_EINVAL, "sgm: workspace too small (%zu < %zu)", workspace_bytes,
                 sgm_workspace_bytes(H, W, D));
-  if ((flags & STM_SGM_FUSED_SWEEPS) && !disp) {
-    // opt-in: two fused raster sweeps (sgm_wave.cu); 1 = shape not handled there
-    const int rc = launch_sgm_wave(cost, image, out, H, W, D, p1, p2, flags, workspace,
-                                   workspace_bytes, stream);
+  const LaneMap m = pick_lane_map(D);
+  if (flags & STM_SGM_FUSED_SWEEPS) {
+    // opt-in: horizontal passes + two fused vertical sweeps (sgm_vsweep.cu); 1 = not handled
+    int rc = 1;
+#define STM_SGM_FS(NV_, VW_)        \
+  if (m.NV == NV_ && m.VW == VW_)   \
+    rc = sgm_fused<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, workspace, workspace_bytes, stream, disp);
+    STM_SGM_FS(1, 4) STM_SGM_FS(2, 4) STM_SGM_FS(1, 2) STM_SGM_FS(3, 2) STM_SGM_FS(1, 1)
+#undef STM_SGM_FS
     if (rc != 1) return rc;
   }
-  const LaneMap m = pick_lane_map(D);
   float *ws = static_cast<float *>(workspace);
   {
     static const char *off = getenv("STM_DEBUG_SGM_CONCURRENT");  // developer knob: "0" disables

@@ -84,6 +84,19 @@ __host__ __device__ inline PathGeom sgm_path_geom(int dir, int idx, int H, int W
   return g;
 }
 
+// Multiplicity of the dir-5 / dir-7 path through pixel (x, y): the table above per pixel.
+__host__ __device__ inline int sgm_mult5(int x, int y, int H, int W) {
+  const int c = x - y, cs = W - H;
+  if (W > H) return (c >= 0 && c < cs) ? 0 : (c == cs ? cs + 1 : 1);
+  if (H > W) return (c > cs && c <= -1) ? 0 : (c == cs ? -cs : 1);
+  return 1;
+}
+__host__ __device__ inline int sgm_mult7(int x, int y, int H, int W) {
+  const int s = x + y;
+  if (W > H) return (s >= H && s <= W - 1) ? 0 : (s == H - 1 ? W - H + 1 : 1);
+  return 1;
+}
+
 // Index of the one path with multiplicity > 1 in dir 5 / dir 7, or -1.
 __host__ __device__ inline int sgm_multi_path_index(int dir, int H, int W) {
   if (dir == 5 && W != H) return (W - H) + (H - 1);

@@ -1,0 +1,679 @@
+// sgm_vsweep.cu -- three SGM directions per pass: the fused vertical sweeps.
+//
+// The six directions with a vertical component (reference src/semiglobal.cpp:18-91: v ^ \v ^\
+// /v ^/) are two groups of three that advance through the image rows together.  A pass per
+// direction reads the cost volume and read-modify-writes the sum volume once per direction
+// (12 B/pix-disp each); a sweep does it once for three directions.
+//
+// Decomposition (what the first two fused designs, profiles/r01_v3_fused_sweeps.md, lacked:
+// thousands of independent chains AND on-chip summation).  Sweep step t is image row
+// y = t (down: directions 2, 4, 6) or y = H-1-t (up: 3, 5, 7).  Warp `u` is a SKEWED column
+// slot: at step t it owns pixel x = (u + t) mod W, so
+//   * the diagonal whose predecessor is (x-1, previous row)  [4 down, 7 up]  stays in the
+//     warp's registers,
+//   * the vertical direction's predecessor (x) belongs to slot u+1, the other diagonal's
+//     (x+1) [6 down, 5 up] to slot u+2 -- both at the PREVIOUS step.
+// Every hand-off therefore points the same way (u <- u+1, u+2): a pipeline, not a lock-step
+// wavefront; slots slip against each other by the hand-off latency instead of waiting for
+// it every row, and there is no chain along a row.  A slot that leaves the image on the right
+// re-enters on the left, where the register-held diagonal starts a new path (L = C); the
+// u+2 diagonal starts a new path at x = W-1.  All W slots do exactly H steps.
+//
+// CTA c owns `ncols` (2..13) consecutive slots, one warp each, plus one importer warp.
+// Inside a CTA slots publish their vertical / diagonal vectors to 4-row rings in shared
+// memory behind relaxed progress flags (no fence: see sgm_wave history, a CTA-scope release
+// compiles to MEMBAR.ALL.CTA and waits for the warp's prefetches).  Between CTAs, slots 0 and
+// 1 write (value, row tag) pairs as single 8-byte words into an L2-resident ring (the tag
+// travels with the data: no fence, no separate flag) and the consumer CTA's importer warp
+// polls them one row ahead and feeds two virtual slots of the shared rings, so compute warps
+// see one interface.  Credits flow back through the progress flags (shared) and a per-CTA
+// imported-rows counter (global).  All CTAs must be co-resident: cooperative launch.
+//
+// Cost and sum vectors of the next PF rows are in flight as per-lane cp.async copies into a
+// private shared-memory ring (a lane only reads back bytes it copied itself: no barrier).
+//
+// Values: same recurrences and same per-direction vectors as sgm.cu; the sum is associated
+// (((S + v) + d1) + d2) per sweep instead of the reference's 0..7 order, and the corner
+// up-diagonals add mult*L in one fused multiply-add instead of mult additions
+// -- within the 1e-4 bar, not bit-identical (STM_SGM_FUSED_SWEEPS is opt-in for that reason).
+#include "lanevec.cuh"
+#include <cstdlib>
+#include <type_traits>
+
+#include "sgm_paths.cuh"
+
+namespace stm {
+namespace vsweep {
+
+constexpr int kCols = 13;      // column slots (compute warps) per CTA; 13 x 148 >= 1920
+constexpr int kR = 4;          // rows in the shared hand-off rings
+constexpr int kRX = 16;        // rows in the CTA->CTA ring
+#ifndef STM_VSWEEP_PF
+#define STM_VSWEEP_PF 5
+#endif
+constexpr int kPfSmall = STM_VSWEEP_PF;
+constexpr int kLook = 4;       // rows of that ring the importer keeps loads in flight for
+constexpr int kFlagStride = 32;  // unsigned per counter: counters of different CTAs never share a line
+constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
+constexpr int kThreads = (kCols + 1) * 32;
+constexpr unsigned kSpinCap = 1u << 24;
+
+template <int DPAD>
+struct Cfg {
+  static constexpr int PF = DPAD <= 192 ? kPfSmall : 4;  // prefetch ring entries per slot (PF-1 rows ahead)
+  static constexpr int kBarOff = 0;                                    // (full, empty)[kCols + 2][kR]
+  static constexpr int kCreditOff = 1008;                              // unsigned: rows the previous CTA has imported
+  static constexpr int kRingBOff = 1024;                               // [kCols+1][kR][DPAD]
+  static constexpr int kRingCOff = kRingBOff + (kCols + 1) * kR * DPAD * 4;  // [kCols+2][kR][DPAD]
+  static constexpr int kPfOff = kRingCOff + (kCols + 2) * kR * DPAD * 4;     // [kCols][PF][2][DPAD]
+  static constexpr int kPfiOff = kPfOff + kCols * PF * 2 * DPAD * 4;         // [kCols][PF][8]
+  static constexpr int kBytes = kPfiOff + kCols * PF * 8 * 4;
+};
+
+struct Params {
+  const float *cost, *image;
+  float *out;
+  int32_t *disp;
+  unsigned long long *xring;  // [G][kRX][3][DPAD] (value, tag) words
+  unsigned *xcons;            // [G][kFlagStride] rows imported so far by CTA c (one 128-byte line each)
+  int H, W, D, G, q, r;       // W = q*G + r: CTAs [0, r) own q+1 slots, the others q
+  int up;                     // 0: directions 2,4,6 top to bottom; 1: 3,5,7 bottom to top
+  int store_vol, emit_wta, defect, min_limit;
+  int dbg;  // developer knob STM_DEBUG_VSWEEP: 1 = importer does not poll, 2 = slots do not wait (wrong results)
+  float p1, p2;
+};
+
+// Developer statistics (STM_DEBUG_VSWEEP & 8), read by stm_debug_vsweep_stats: clock64 cycles.
+__device__ unsigned long long g_stats[64];
+// Trace of one CTA (STM_DEBUG_VSWEEP & 16): clock64 of [warp][row - kTraceRow0][event].
+constexpr int kTraceRow0 = 500, kTraceRows = 24, kTraceCta = 5;
+__device__ long long g_trace[16][kTraceRows][4];
+__device__ __forceinline__ void stat_add(int i, unsigned long long v) { atomicAdd(&g_stats[i], v); }
+
+// ---- flags ----------------------------------------------------------------------------------
+// Hand-offs inside a CTA: one (full, empty) mbarrier pair per slot and ring row.  A waiting warp
+// is suspended by the hardware (try_wait) instead of spinning: spinning neighbours were measured
+// to take the issue slots of the one warp everybody is waiting for.
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}" :: "r"(bar), "r"(parity) : "memory");
+}
+// barrier addresses: full(s, e) and empty(s, e) for slot s (0..kCols+1) and ring row e
+__device__ __forceinline__ unsigned bar_full(unsigned base, int s, int e) { return base + (unsigned)((s * kR + e) * 16); }
+__device__ __forceinline__ unsigned bar_empty(unsigned base, int s, int e) { return base + (unsigned)((s * kR + e) * 16 + 8); }
+// readers of slot s's ring rows: slot s-1 takes the vertical vector, slot s-2 the diagonal
+__device__ __forceinline__ int slot_readers(int s, int ncols) {
+  return ((s - 1 >= 0 && s - 1 < ncols) ? 1 : 0) + ((s - 2 >= 0 && s - 2 < ncols) ? 1 : 0);
+}
+__device__ __forceinline__ unsigned ld_flag_s(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.relaxed.cta.shared.u32 %0, [%1];"
+               : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_flag_s(unsigned *p, unsigned v) {
+  asm volatile("st.relaxed.cta.shared.u32 [%0], %1;"
+               :: "r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_relaxed_g(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_g(unsigned *p, unsigned v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+// ---- (value, tag) words ---------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long ll_pack(float v, unsigned tag) {
+  return ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+}
+template <int NV, int VW>
+__device__ __forceinline__ void lv_st_ll(const LaneVec<NV, VW> &a, unsigned long long *p, int lane,
+                                         unsigned tag) {
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    unsigned long long *q = p + k * 32 * VW + lane * VW;
+    if constexpr (VW % 2 == 0) {
+#pragma unroll
+      for (int j = 0; j < VW; j += 2)
+        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};"
+                     :: "l"(q + j), "l"(ll_pack(a.v[k][j], tag)), "l"(ll_pack(a.v[k][j + 1], tag))
+                     : "memory");
+    } else {
+      asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(q), "l"(ll_pack(a.v[k][0], tag))
+                   : "memory");
+    }
+  }
+}
+template <int NV, int VW>
+__device__ __forceinline__ void lv_ld_ll(unsigned long long (&w)[NV * VW], const unsigned long long *p,
+                                         int lane) {
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const unsigned long long *q = p + k * 32 * VW + lane * VW;
+    if constexpr (VW % 2 == 0) {
+#pragma unroll
+      for (int j = 0; j < VW; j += 2)
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];"
+                     : "=l"(w[k * VW + j]), "=l"(w[k * VW + j + 1]) : "l"(q + j) : "memory");
+    } else {
+      asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w[k * VW]) : "l"(q) : "memory");
+    }
+  }
+}
+
+// ---- shared-memory vectors ------------------------------------------------------------------
+template <int NV, int VW>
+__device__ __forceinline__ void lv_lds(LaneVec<NV, VW> &r, const float *p, int lane) {
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const float *q = p + k * 32 * VW + lane * VW;
+    if constexpr (VW == 4) {
+      const float4 t = *reinterpret_cast<const float4 *>(q);
+      r.v[k][0] = t.x; r.v[k][1] = t.y; r.v[k][2] = t.z; r.v[k][3] = t.w;
+    } else if constexpr (VW == 2) {
+      const float2 t = *reinterpret_cast<const float2 *>(q);
+      r.v[k][0] = t.x; r.v[k][1] = t.y;
+    } else {
+      r.v[k][0] = *q;
+    }
+  }
+}
+template <int NV, int VW>
+__device__ __forceinline__ void lv_sts(const LaneVec<NV, VW> &r, float *p, int lane) {
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    float *q = p + k * 32 * VW + lane * VW;
+    if constexpr (VW == 4) *reinterpret_cast<float4 *>(q) = make_float4(r.v[k][0], r.v[k][1], r.v[k][2], r.v[k][3]);
+    else if constexpr (VW == 2) *reinterpret_cast<float2 *>(q) = make_float2(r.v[k][0], r.v[k][1]);
+    else *q = r.v[k][0];
+  }
+}
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async(float *smem_dst, const float *gmem_src) {
+  if constexpr (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                 :: "r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;"
+                 :: "r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src), "n"(BYTES)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory");
+}
+
+// ---- importer: next CTA's slots 0 and 1 -> virtual slots ncols, ncols+1 ----------------------
+template <int NV, int VW>
+__device__ void importer_warp(unsigned char *smem, const Params &P, int ncols, int lane) {
+  constexpr int DPAD = NV * 32 * VW, NE = NV * VW;
+  using C = Cfg<DPAD>;
+  const int nrows = P.H - 1;  // the last row's vectors have no consumer
+  if (nrows <= 0) return;
+  const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
+  float *ringB = reinterpret_cast<float *>(smem + C::kRingBOff);
+  float *ringC = reinterpret_cast<float *>(smem + C::kRingCOff);
+  const int c = blockIdx.x;
+  const int nb = c + 1 == P.G ? 0 : c + 1;
+  const unsigned long long *src = P.xring + (size_t)nb * kRX * 3 * DPAD;
+  float *dst[3] = {ringB + (size_t)ncols * kR * DPAD, ringC + (size_t)ncols * kR * DPAD,
+                   ringC + (size_t)(ncols + 1) * kR * DPAD};
+
+  unsigned long long buf[kLook][3][NE];
+  auto load = [&](unsigned long long (&w)[3][NE], int row) {
+    const unsigned long long *s = src + (size_t)(row & (kRX - 1)) * 3 * DPAD;
+#pragma unroll
+    for (int v = 0; v < 3; ++v) lv_ld_ll<NV, VW>(w[v], s + v * DPAD, lane);
+  };
+  auto ready = [&](const unsigned long long (&w)[3][NE], int row) {
+    bool ok = true;
+#pragma unroll
+    for (int v = 0; v < 3; ++v)
+#pragma unroll
+      for (int e = 0; e < NE; ++e) ok = ok && (unsigned)(w[v][e] >> 32) == (unsigned)(row + 1);
+    return __all_sync(FULL, ok) != 0;
+  };
+
+  const bool poll = !(P.dbg & 1), stats = (P.dbg & 8) != 0;
+  unsigned long long st_polls = 0, st_ready = 0, st_credit = 0, st_rtt = 0;
+  // The slots that export (0, 1) have prefetches in flight and were measured to wait ~6 us for
+  // a global flag read; the importer has none, so it fetches their credit (rows the PREVIOUS
+  // CTA has imported) every row, one row ahead of publishing it in shared memory.
+  const unsigned *xcred_src = &P.xcons[(size_t)(c == 0 ? P.G - 1 : c - 1) * kFlagStride];
+  unsigned *xcred_dst = reinterpret_cast<unsigned *>(smem + C::kCreditOff);
+  unsigned cred = ld_relaxed_g(xcred_src);
+  // kLook rows of (value, tag) words in flight: the L2 round trip is longer than a row
+#pragma unroll
+  for (int i = 0; i < kLook; ++i) load(buf[i], i < nrows ? i : nrows - 1);
+#pragma unroll 1
+  for (int r0 = 0; r0 < nrows; r0 += kLook) {
+#pragma unroll
+    for (int i = 0; i < kLook; ++i) {
+      const int r = r0 + i;
+      if (r < nrows) {
+        const int rr = r & (kR - 1);
+        if (lane == 0) st_flag_s(xcred_dst, cred);
+        cred = ld_relaxed_g(xcred_src);
+        long long c0 = (stats || (P.dbg & 16)) ? clock64() : 0;
+        if (r >= kR && poll) {  // the readers of ring row r-kR are done with it
+          const unsigned par = (unsigned)(((r >> 2) - 1) & 1);
+          mbar_wait(bar_empty(bars, ncols, rr), par);
+          mbar_wait(bar_empty(bars, ncols + 1, rr), par);
+        }
+        long long c1 = (stats || (P.dbg & 16)) ? clock64() : 0;
+        unsigned tries = 0;
+        while (poll && !ready(buf[i], r)) {
+          if (++tries > kSpinCap) __trap();
+          const long long r0 = stats ? clock64() : 0;
+          if (lane == 0) st_flag_s(xcred_dst, cred);
+          cred = ld_relaxed_g(xcred_src);
+          load(buf[i], r);
+          if (stats) { (void)ready(buf[i], r); st_rtt += clock64() - r0; }
+        }
+        if (stats) { st_credit += c1 - c0; st_ready += clock64() - c1; st_polls += tries; }
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+          LaneVec<NV, VW> t;
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+#pragma unroll
+            for (int j = 0; j < VW; ++j) t.v[k][j] = __uint_as_float((unsigned)buf[i][v][k * VW + j]);
+          lv_sts<NV, VW>(t, dst[v] + rr * DPAD, lane);
+        }
+        mbar_arrive(bar_full(bars, ncols, rr));
+        mbar_arrive(bar_full(bars, ncols + 1, rr));
+        if ((P.dbg & 16) && c == kTraceCta && lane == 0 && r >= kTraceRow0 && r < kTraceRow0 + kTraceRows) {
+          g_trace[15][r - kTraceRow0][0] = c1; g_trace[15][r - kTraceRow0][1] = clock64();
+        }
+        __syncwarp();
+        if (lane == 0) st_relaxed_g(&P.xcons[(size_t)c * kFlagStride], (unsigned)(r + 1));
+        const int rn = r + kLook;
+        load(buf[i], rn < nrows ? rn : nrows - 1);
+      }
+    }
+  }
+  // the exporters' last credit: the previous CTA has imported row H-2-kRX
+  for (unsigned tries = 0;; ++tries) {
+    if (lane == 0) st_flag_s(xcred_dst, cred);
+    if ((int)cred >= nrows - kRX) break;
+    if (tries > kSpinCap) __trap();
+    cred = ld_relaxed_g(xcred_src);
+  }
+  if (stats && lane == 0) {
+    stat_add(0, (unsigned long long)nrows); stat_add(1, st_polls); stat_add(2, st_ready);
+    stat_add(3, st_credit); stat_add(4, st_rtt);
+  }
+}
+
+// ---- one column slot ------------------------------------------------------------------------
+template <int NV, int VW>
+__device__ __forceinline__ void add_weighted(LaneVec<NV, VW> &o, const LaneVec<NV, VW> &L, int mult) {
+  if (mult == 1) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+  } else if (mult != 0) {
+    const float w = (float)mult;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int j = 0; j < VW; ++j) o.v[k][j] = __fmaf_rn(w, L.v[k][j], o.v[k][j]);
+  }
+}
+
+template <int NV, int VW>
+__device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int base, int j, int lane) {
+  constexpr int DPAD = NV * 32 * VW;
+  using C = Cfg<DPAD>;
+  constexpr int PF = C::PF;
+  const int H = P.H, W = P.W, D = P.D, up = P.up;
+  const float p1 = P.p1, p2 = P.p2;
+  const LaneCtx cx = lv_ctx<NV, VW>(lane, P.min_limit);
+  const int lane_off = lane * VW;
+  // shared memory, all pre-offset by this slot and lane
+  const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
+  const bool has_readers = j >= 1;
+  const unsigned *xcredit = reinterpret_cast<const unsigned *>(smem + C::kCreditOff);
+  float *ringB = reinterpret_cast<float *>(smem + C::kRingBOff) + (size_t)j * kR * DPAD + lane_off;
+  float *ringC = reinterpret_cast<float *>(smem + C::kRingCOff) + (size_t)j * kR * DPAD + lane_off;
+  float *pf = reinterpret_cast<float *>(smem + C::kPfOff) + (size_t)j * PF * 2 * DPAD + lane_off;
+  // lanes take one of four intensity roles (lane & 3): 1, 2, 3 = the pixel behind at x-1, x, x+1
+  // (directions A, B, C); role 0 repeats role 2.  Same role, same value: the copies may collide.
+  const int role = lane & 3;
+  const int dxp = role == 0 ? 0 : role - 2;
+  float *pfi = reinterpret_cast<float *>(smem + C::kPfiOff) + j * PF * 8 + role * 2;
+
+  const long long rowstep = up ? -(long long)W : (long long)W;
+  int x = base + j, y = up ? H - 1 : 0;
+  // fetch side: row pointers (lane offset included) + column
+  const float *crow = P.cost + (long long)y * W * D + lane_off;
+  const float *srow = P.out + (long long)y * W * D + lane_off;
+  const float *irow = P.image + (long long)y * W, *iprev = irow;
+  const long long rowstep_d = rowstep * D;
+  int fx = x, ft = 0;
+
+  // row ft: cost, sum and intensities into ring entry `e`; always exactly one commit group.
+  // Past the last row the last row is fetched again (never used).
+  auto issue = [&](int e) {
+    const float *cs = crow + (long long)fx * D, *ss = srow + (long long)fx * D;
+    float *dc = pf + e * 2 * DPAD;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int off = k * 32 * VW;
+      if (VW > 1 || off + lane < D) {
+        cp_async<VW * 4>(dc + off, cs + off);
+        cp_async<VW * 4>(dc + DPAD + off, ss + off);
+      }
+    }
+    int pc = fx + dxp;
+    pc = pc < 0 ? 0 : (pc > W - 1 ? W - 1 : pc);
+    cp_async<4>(pfi + e * 8, irow + fx);
+    cp_async<4>(pfi + e * 8 + 1, iprev + pc);
+    cp_async_commit();
+    if (ft + 1 < H) {
+      ++ft;
+      iprev = irow; irow += rowstep; crow += rowstep_d; srow += rowstep_d;
+      fx = fx + 1 == W ? 0 : fx + 1;
+    }
+  };
+#pragma unroll 1
+  for (int i = 0; i < PF; ++i) issue(i);
+
+  LaneVec<NV, VW> LA;
+  unsigned xc_seen = 0;
+  unsigned long long *xdst = P.xring + (size_t)blockIdx.x * kRX * 3 * DPAD + lane_off;
+  float *orow = P.out + (long long)y * W * D + lane_off;
+  int32_t *drow = P.disp + (long long)y * W;
+  const bool sync = !(P.dbg & 2), stats = (P.dbg & 8) != 0;
+  unsigned long long st_dep = 0, st_cred = 0, st_g = 0, st_gn = 0;
+  const long long st_begin = clock64();
+  const bool store_vol = P.store_vol != 0, emit_wta = P.emit_wta != 0, defect = P.defect != 0;
+  int e = 0;
+
+  // penalties of the row about to be processed, computed one row ahead (off the hand-off path)
+  float pa = 0.f, pb = 0.f, pc = 0.f;
+
+  const bool trace = (P.dbg & 16) && blockIdx.x == kTraceCta && lane == 0;
+  auto mark = [&](int t, int ev) {
+    if (trace && t >= kTraceRow0 && t < kTraceRow0 + kTraceRows) g_trace[j][t - kTraceRow0][ev] = clock64();
+  };
+
+  auto row = [&](auto first_tag, int t) {
+    constexpr bool FIRST = decltype(first_tag)::value;
+    cp_async_wait<PF - 2>();  // rows t and t+1 have landed
+    LaneVec<NV, VW> c, o;
+    lv_lds<NV, VW>(c, pf + e * 2 * DPAD, 0);
+    lv_lds<NV, VW>(o, pf + e * 2 * DPAD + DPAD, 0);
+    if constexpr (VW == 1) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+        if (k * 32 + lane >= D) { c.v[k][0] = CUDART_INF_F; o.v[k][0] = 0.f; }
+    }
+    const int en = e + 1 == PF ? 0 : e + 1;
+    const float2 ii = *reinterpret_cast<const float2 *>(pfi + en * 8);  // row t+1
+    asm volatile("" ::: "memory");
+    issue(e);  // refill this entry with row t + PF
+    e = en;
+
+    LaneVec<NV, VW> LB, LC;
+    if constexpr (FIRST) {
+      LB = c; LC = c;
+    } else {
+      const int er = (t - 1) & (kR - 1);
+      const unsigned parr = (unsigned)(((t - 1) >> 2) & 1);
+      mark(t, 0);
+      if (sync) {
+        const long long c0 = stats ? clock64() : 0;
+        mbar_wait(bar_full(bars, j + 1, er), parr);
+        mbar_wait(bar_full(bars, j + 2, er), parr);
+        if (stats) st_dep += clock64() - c0;
+      }
+      mark(t, 1);
+      lv_lds<NV, VW>(LB, ringB + kR * DPAD + er * DPAD, 0);
+      lv_lds<NV, VW>(LC, ringC + 2 * kR * DPAD + er * DPAD, 0);
+      mbar_arrive(bar_empty(bars, j + 1, er));
+      mbar_arrive(bar_empty(bars, j + 2, er));
+      // straight-line so the two recurrences interleave; the path start is a select
+      lv_sgm_step<NV, VW>(LB, c, p1, pb, cx);
+      lv_sgm_step<NV, VW>(LC, c, p1, pc, cx);
+      const bool startC = x == W - 1;
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int q = 0; q < VW; ++q) LC.v[k][q] = startC ? c.v[k][q] : LC.v[k][q];
+    }
+
+    {  // hand the vertical and the u+2 diagonal to slots j-1, j-2 (the last row's go nowhere)
+      const int ew = t & (kR - 1);
+      if (t >= kR && has_readers && sync) {  // ring row t-kR has been read by slots j-1, j-2
+        const long long c0 = stats ? clock64() : 0;
+        mbar_wait(bar_empty(bars, j, ew), (unsigned)(((t >> 2) - 1) & 1));
+        if (stats) st_cred += clock64() - c0;
+      }
+      lv_sts<NV, VW>(LB, ringB + ew * DPAD, 0);
+      lv_sts<NV, VW>(LC, ringC + ew * DPAD, 0);
+      mbar_arrive(bar_full(bars, j, ew));
+      mark(t, 2);
+      if (j < 2 && t < H - 1) {  // and to the previous CTA
+        if (t >= kRX) {
+          const unsigned need_x = (unsigned)(t - kRX + 1);
+          if (xc_seen < need_x && sync) {
+            const long long c0 = stats ? clock64() : 0;
+            unsigned tries = 0;
+            while ((xc_seen = ld_flag_s(xcredit)) < need_x) {
+              __nanosleep(100);
+              if (++tries > kSpinCap) __trap();
+            }
+            if (stats) { st_g += clock64() - c0; st_gn += 1; }
+          }
+        }
+        unsigned long long *ex = xdst + (size_t)(t & (kRX - 1)) * 3 * DPAD;
+        if (j == 0) {
+          lv_st_ll<NV, VW>(LB, ex, 0, (unsigned)(t + 1));
+          lv_st_ll<NV, VW>(LC, ex + DPAD, 0, (unsigned)(t + 1));
+        } else {
+          lv_st_ll<NV, VW>(LC, ex + 2 * DPAD, 0, (unsigned)(t + 1));
+        }
+      }
+    }
+
+    // Off the hand-off path, one block: the register-held diagonal (nobody's input), the next
+    // row's penalties and this row's sum / store / argmin.
+    if constexpr (FIRST) {
+      LA = c;
+    } else {
+      LaneVec<NV, VW> LAs = LA;
+      lv_sgm_step<NV, VW>(LAs, c, p1, pa, cx);
+      const bool startA = x == 0;
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int q = 0; q < VW; ++q) LA.v[k][q] = startA ? c.v[k][q] : LAs.v[k][q];
+    }
+    {
+      const float adj = sgm_p2_adjusted(p1, p2, ii.x, ii.y);
+      pa = __shfl_sync(FULL, adj, 1); pb = __shfl_sync(FULL, adj, 2); pc = __shfl_sync(FULL, adj, 3);
+    }
+
+    // sum in the reference's direction order: down 2, 4, 6 = B, A, C; up 3, 5, 7 = B, C, A
+    add_weighted<NV, VW>(o, LB, 1);
+    if (!up) {
+      add_weighted<NV, VW>(o, LA, 1);
+      add_weighted<NV, VW>(o, LC, 1);
+    } else if (!defect) {
+      add_weighted<NV, VW>(o, LC, 1);
+      add_weighted<NV, VW>(o, LA, 1);
+    } else {
+      add_weighted<NV, VW>(o, LC, sgm_mult5(x, y, H, W));
+      add_weighted<NV, VW>(o, LA, sgm_mult7(x, y, H, W));
+    }
+    if (store_vol) lv_store<NV, VW, true>(o, orow + (long long)x * D, 0, D - lane_off);
+    if (emit_wta) lv_argmin_store<NV, VW>(o, lane, D, drow + x);
+
+    mark(t, 3);
+    x = x + 1 == W ? 0 : x + 1;
+    y += up ? -1 : 1;
+    orow += rowstep_d; drow += rowstep;
+  };
+
+  row(std::true_type{}, 0);
+#pragma unroll 1
+  for (int t = 1; t < H; ++t) row(std::false_type{}, t);
+  cp_async_wait<0>();
+  if (stats && lane == 0) {
+    stat_add(8 + j, st_dep); stat_add(24 + j, st_cred); stat_add(40, st_g); stat_add(41, st_gn);
+    stat_add(42, (unsigned long long)(clock64() - st_begin)); stat_add(43, 1ull);
+  }
+}
+
+template <int NV, int VW>
+__global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  using C = Cfg<NV * 32 * VW>;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int c = blockIdx.x;
+  const int ncols = P.q + (c < P.r ? 1 : 0);
+  const int base = c * P.q + (c < P.r ? c : P.r);
+  if (threadIdx.x < (kCols + 2) * kR) {
+    const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
+    const int sl = threadIdx.x / kR, e = threadIdx.x % kR;
+    const int readers = slot_readers(sl, ncols);
+    mbar_init(bar_full(bars, sl, e), 32u);                             // every lane of the writer
+    mbar_init(bar_empty(bars, sl, e), readers ? 32u * readers : 1u);   // every lane of each reader
+  }
+  if (threadIdx.x == 0) *reinterpret_cast<unsigned *>(smem + C::kCreditOff) = 0u;
+  __syncthreads();
+  if (wid == kCols) importer_warp<NV, VW>(smem, P, ncols, lane);
+  else if (wid < ncols) column_warp<NV, VW>(smem, P, ncols, base, wid, lane);
+}
+
+static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
+
+// CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.
+template <int NV, int VW>
+static int ctas(int W) {
+  using C = Cfg<NV * 32 * VW>;
+  static int cap = -1;  // per instantiation
+  if (cap < 0) {
+    auto kernel = sgm_vsweep_kernel<NV, VW>;
+    int per_sm = 0;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kBytes) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, C::kBytes) != cudaSuccess) {
+      cudaGetLastError();
+      return 0;
+    }
+    cap = per_sm * num_sms();
+  }
+  int G = cap < kMaxCtas ? cap : kMaxCtas;
+  if (G > W / 2) G = W / 2;
+  if (G < 1 || (W + G - 1) / G > kCols) return 0;
+  return G;
+}
+
+template <int NV, int VW>
+static int run(const float *cost, const float *image, float *out, int32_t *disp, int H, int W, int D,
+               float p1, float p2, int min_limit, int up, bool store_vol, char *ws,
+               cudaStream_t stream) {
+  constexpr int DPAD = NV * 32 * VW;
+  using C = Cfg<DPAD>;
+  static_assert(C::kBytes <= 227 * 1024, "shared memory budget");
+  auto kernel = sgm_vsweep_kernel<NV, VW>;
+  const int G = ctas<NV, VW>(W);
+  if (G < 1) return 1;
+  Params P;
+  P.cost = cost; P.image = image; P.out = out; P.disp = disp;
+  P.xcons = reinterpret_cast<unsigned *>(ws);
+  P.xring = reinterpret_cast<unsigned long long *>(ws + align256(kMaxCtas * kFlagStride * sizeof(unsigned)));
+  P.H = H; P.W = W; P.D = D; P.G = G; P.q = W / G; P.r = W % G;
+  P.up = up; P.store_vol = store_vol ? 1 : 0; P.emit_wta = disp ? 1 : 0;
+  P.defect = (up && W != H) ? 1 : 0;
+  P.min_limit = min_limit; P.p1 = p1; P.p2 = p2;
+  static const char *dbg = getenv("STM_DEBUG_VSWEEP");
+  P.dbg = dbg ? atoi(dbg) : 0;
+  // tags are row numbers: clear the counters and the rings this launch will use
+  STM_CUDA_TRY(cudaMemsetAsync(ws, 0, align256(kMaxCtas * kFlagStride * sizeof(unsigned)) +
+                                          (size_t)G * kRX * 3 * DPAD * sizeof(unsigned long long), stream));
+  void *args[] = {&P};
+  STM_CUDA_TRY(cudaLaunchCooperativeKernel((const void *)kernel, dim3(G), dim3(kThreads), args,
+                                           (size_t)C::kBytes, stream));
+  return check_launch("sgm_vsweep_kernel");
+}
+
+}  // namespace vsweep
+
+extern "C" __attribute__((visibility("default"))) int stm_debug_vsweep_trace(long long *out) {
+  return cudaMemcpyFromSymbol(out, vsweep::g_trace, sizeof(long long) * 16 * vsweep::kTraceRows * 4) == cudaSuccess ? 0 : -1;
+}
+
+// Developer hook (tools/vsweep_probe.py): copies and clears the statistics counters.
+extern "C" __attribute__((visibility("default"))) int stm_debug_vsweep_stats(unsigned long long *out64) {
+  if (cudaMemcpyFromSymbol(out64, vsweep::g_stats, sizeof(unsigned long long) * 64) != cudaSuccess) return -1;
+  static unsigned long long zero[64];
+  return cudaMemcpyToSymbol(vsweep::g_stats, zero, sizeof(zero)) == cudaSuccess ? 0 : -1;
+}
+
+static bool vsweep_lane_map(int D) {
+  const LaneMap m = pick_lane_map(D);
+  return (m.VW == 4 && m.NV <= 2) || (m.VW == 2 && (m.NV == 1 || m.NV == 3)) || (m.VW == 1 && m.NV == 1);
+}
+
+size_t sgm_vsweep_workspace_bytes(int H, int W, int D) {
+  if (H < 2 || W < 2 || !vsweep_lane_map(D)) return 0;
+  const LaneMap m = pick_lane_map(D);
+  const size_t dpad = (size_t)m.NV * 32 * m.VW;
+  return vsweep::align256(vsweep::kMaxCtas * vsweep::kFlagStride * sizeof(unsigned)) +
+         (size_t)vsweep::kMaxCtas * vsweep::kRX * 3 * dpad * sizeof(unsigned long long);
+}
+
+// Whether launch_sgm_vsweep will take this shape on the current device.
+bool sgm_vsweep_can_run(int H, int W, int D) {
+  if (H < 2 || W < 2 || !vsweep_lane_map(D)) return false;
+  const LaneMap m = pick_lane_map(D);
+#define STM_VSWEEP_CASE(NV_, VW_) \
+  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W) > 0;
+  STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
+  STM_VSWEEP_CASE(1, 1)
+#undef STM_VSWEEP_CASE
+  return false;
+}
+
+// One fused sweep: out += L2+L4+L6 (up = 0) or L3+L5+L7 (up = 1, reference multiplicities),
+// optionally without writing the sums back (store_vol = false) and/or emitting the disparity
+// map.  Returns 1 when the shape is not handled here (the caller runs the directions one by one).
+int launch_sgm_vsweep(const float *cost, const float *image, float *out, int32_t *disp, int H, int W,
+                      int D, float p1, float p2, int min_limit, int up, bool store_vol,
+                      void *workspace, size_t workspace_bytes, cudaStream_t stream) {
+  if (H < 2 || W < 2 || !vsweep_lane_map(D)) return 1;
+  if (workspace == nullptr || workspace_bytes < sgm_vsweep_workspace_bytes(H, W, D)) return 1;
+  if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) |
+       reinterpret_cast<uintptr_t>(workspace)) & 15)
+    return 1;
+  const LaneMap m = pick_lane_map(D);
+  char *ws = static_cast<char *>(workspace);
+#define STM_VSWEEP_CASE(NV_, VW_)      \
+  if (m.NV == NV_ && m.VW == VW_)      \
+    return vsweep::run<NV_, VW_>(cost, image, out, disp, H, W, D, p1, p2, min_limit, up, store_vol, ws, stream);
+  STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
+  STM_VSWEEP_CASE(1, 1)
+#undef STM_VSWEEP_CASE
+  return 1;
+}
+
+}  // namespace stm

@@ -19,9 +19,12 @@ class Semiglobal:
     (SURVEY F6); True takes the min over all D like the reference CUDA kernel.
     Unlike the reference's CUDA branch, D does not have to be a power of two.
     The default runs one kernel per direction and adds the eight directions into the output
-    in the reference's order.  fused_sweeps=True (experimental) computes them in two raster
-    sweeps: a quarter of the HBM traffic and the same values within a few ulp, but it is
-    latency-bound and currently about 5x slower.  concurrent_directions=True (default) lets
+    in the reference's order.  fused_sweeps=True keeps the two horizontal passes and computes
+    the six directions with a vertical component as two fused sweeps (csrc/sgm_vsweep.cu):
+    four passes over the volumes instead of eight, same per-direction values, but the sum is
+    associated per sweep (2,4,6 then 3,5,7) -- within 1e-4 of the reference order, not
+    bit-identical.  Shapes the sweeps do not handle (more than 13 columns per SM, D not in
+    {<=32, 64, 128, 192, 256}) silently take the per-direction passes.  concurrent_directions=True (default) lets
     small landscape / square volumes (<= 48 MB, latency-bound) run the eight directions at
     the same time into per-direction buffers that are then added in the reference's order --
     bit-identical to the sequential passes, which concurrent_directions=False forces.
@@ -71,6 +74,8 @@ class Semiglobal:
             flags |= STM_SGM_DISPARITY_ONLY
         if not self.concurrent_directions:
             flags |= STM_SGM_SEQUENTIAL
+        if self.fused_sweeps:
+            flags |= STM_SGM_FUSED_SWEEPS
         _AggregationOps.run_semiglobal_wta(cost_volume, left_image, self.penalty1, self.penalty2,
                                            sga_volume, disparity_img, flags)
         return sga_volume, disparity_img

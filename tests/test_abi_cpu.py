@@ -41,11 +41,12 @@ def test_workspace_query_is_pure():
     lib.stm_sgm_workspace_bytes.restype = ctypes.c_size_t
 
     def expect(H, W, dpad):
-        # csrc/sgm_wave.cu: [l-store dir 5][l-store dir 7][CTA->CTA rings: ceil(H/4) x 32 slots
-        # x 3 vectors][flags: 2 sweeps x {gprog, gcons} x ceil(H/4)], each 16-byte aligned
-        a16 = lambda n: (n + 15) // 16 * 16
-        g = (H + 3) // 4
-        return 2 * a16(min(H, W) * dpad * 4) + a16(g * 32 * 3 * dpad * 4) + a16(4 * g * 4)
+        # max of csrc/sgm.cu (one path's vectors for the corner-diagonal replay) and
+        # csrc/sgm_vsweep.cu (192 imported-row counters of 128 B + 192 CTA->CTA rings of
+        # 16 rows x 3 vectors of 8-byte (value, tag) words; only for the lane maps it handles)
+        direction = min(H, W) * dpad * 4
+        sweeps = 24576 + 192 * 16 * 3 * dpad * 8 if (H >= 2 and W >= 2 and dpad in (32, 64, 128, 192, 256)) else 0
+        return max(direction, sweeps)
 
     assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == expect(1080, 1920, 128)
     assert lib.stm_sgm_workspace_bytes(30, 18, 16) == expect(30, 18, 32)  # D=16 pads to 32 lanes

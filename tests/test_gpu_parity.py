@@ -154,10 +154,13 @@ def test_sgm_horizontal_bulk_copy_kernel_tiles(sm, H, W, D):
 
 
 @pytest.mark.parametrize("H,W,D", [(70, 150, 128), (150, 70, 64), (45, 333, 192), (33, 100, 32),
-                                     (64, 64, 128), (5, 700, 64), (130, 9, 16)])
+                                     (64, 64, 128), (5, 700, 64), (130, 9, 16), (24, 1900, 64),
+                                     (40, 1920, 128), (37, 301, 256), (3, 2, 32), (2, 5, 64)])
 def test_sgm_sweeps_many_ctas_and_ring_wraps(sm, H, W, D):
-    """Shapes with many CTAs (rows / 4) and rows longer than every hand-off ring (8 / 16
-    slots in shared memory, 32 in global memory), landscape, portrait and square."""
+    """Fused vertical sweeps (csrc/sgm_vsweep.cu): one CTA to 148 CTAs, 2 to 13 column slots
+    per CTA, more rows than every hand-off ring (4 rows in shared memory, 16 in global memory),
+    slots that wrap around the image edge, landscape (defective up-diagonals),
+    portrait and square."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H + 3 * W, scale="unit")
     cost = O.ssd(left, right, D, 3)
     want = O.sgm(cost, left, 0.1, 0.2)
@@ -521,10 +524,27 @@ def test_full_size_1080p_properties(sm):
     assert bool(torch.equal(d1, d2)) and int(d1.min()) >= 0 and int(d1.max()) < D
 
 
+@pytest.mark.parametrize("H,W,D", [(30, 47, 128), (47, 30, 64), (21, 21, 32), (19, 333, 192)])
+def test_sgm_fused_sweeps_fold_winner_takes_all(sm, H, W, D):
+    """stm_sgm_wta_f32 with STM_SGM_FUSED_SWEEPS: the up sweep emits the disparity map; it is
+    exactly WinnerTakesAll of the volume the same call returns, the volume meets the oracle
+    bar, and STM_SGM_DISPARITY_ONLY (no write-back) gives the same map."""
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 5 + W, scale="unit")
+    cost = O.ssd(left, right, D, 3)
+    c, l = cuda(cost), cuda(left)
+    fused = sm.aggregation.Semiglobal(fused_sweeps=True)
+    vol, disp = fused.aggregate_and_reduce(c, l)
+    assert_volume_close(vol, O.sgm(cost, left, 0.1, 0.2))
+    assert torch.equal(disp, sm.disparity_reduce.WinnerTakesAll()(vol))
+    assert torch.equal(vol, fused(c, l))
+    _, disp2 = fused.aggregate_and_reduce(c, l, keep_volume=False)
+    assert torch.equal(disp2, disp)
+
+
 @pytest.mark.parametrize("fused_sweeps", [False, True])
 def test_full_height_sgm_column_strip_vs_oracle(sm, fused_sweeps):
     """Full-height (1080 rows), narrow strip: exercises long paths and the 1080-fold
-    corner-diagonal multiplicity against the oracle (270 CTAs in the fused-sweep mode)."""
+    corner-diagonal multiplicity against the oracle (12 CTAs in the fused-sweep mode)."""
     H, W, D = 1080, 24, 32
     left, right, _ = synth.random_dot_pair(H, W, D, seed=77, scale="unit")
     cost = O.ssd(left, right, D, 3)
