@@ -299,10 +299,12 @@ def run_b200_arm(args):
         except Exception:
             traffic = None
     passes = []
+    fused = len(pass_ms) == 4  # horizontal passes + two fused vertical sweeps (sgm_vsweep.cu)
     for (k, d), ts in sorted(pass_ms.items()):
         t = sorted(ts)[len(ts) // 2]
-        b = sgm_pass_bytes(d, k == 0, H, W, D)
-        passes.append({"dir": d, "ms": round(t, 4), "bytes": b, "GBs": round(b / (t * 1e-3) / 1e9, 1),
+        b = sgm_pass_bytes(d, k == 0, H, W, D, fused_sweep=fused and k >= 2)
+        label = {2: "2+4+6", 3: "3+5+7"}[d] if fused and k >= 2 else str(d)
+        passes.append({"dir": label, "ms": round(t, 4), "bytes": b, "GBs": round(b / (t * 1e-3) / 1e9, 1),
                        "frac_of_peak": round(b / (t * 1e-3) / 1e9 / peak, 3)})
     stages = {k: {"ms": round(v, 4), "algo_GBs": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9, 1),
                   "frac": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9 / peak, 4)}
@@ -320,7 +322,8 @@ def run_b200_arm(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
         "ms_per_frame": ms / args.steps / F, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "1920x1080 D=128 SSD(k=7)+SGM(P1=.1,P2=.2, reference path set)+WTA, "
+        "config": {"workload": "1920x1080 D=128 SSD(k=7)+SGM(P1=.1,P2=.2, reference path set; 2 horizontal "
+                               "passes + 2 fused vertical sweeps)+WTA, "
                                "random-dot stereograms", "frames_per_gpu_per_step": F,
                    "frames_in_flight": 2,
                    "sharding": f"frame-sharded x{world}, no collective",
@@ -333,8 +336,8 @@ def run_b200_arm(args):
         "roofline": {"bound": "hbm", "kernel": f"{dom} stage ({sgm_launches} launches)" if dom == "sgm" else dom,
                      "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
-                     # what each launch of the per-direction design HAS to move (C read, S
-                     # read-modify-write; the first pass only writes) over its own duration
+                     # what each pass of the stage HAS to move (C read, S read-modify-write;
+                     # the first pass only writes) over its own duration
                      "passes": passes},
         "stages": stages,
         "cpu_baseline": cpu_baseline,
@@ -345,11 +348,14 @@ def run_b200_arm(args):
     return 0
 
 
-def sgm_pass_bytes(direction, first, H, W, D):
-    """Bytes one direction pass must move in the per-direction design: read C, read and write
-    S (the first pass only writes S), read the intensity, for the pixels the direction visits
-    (the defective up-diagonals 5 and 7 skip a band of a landscape image)."""
+def sgm_pass_bytes(direction, first, H, W, D, fused_sweep=False):
+    """Bytes one pass must move: read C, read and write S (the first pass only writes S), read
+    the intensity, for the pixels the pass visits (the defective up-diagonals 5 and 7 skip a
+    band of a landscape image; a fused sweep of three directions visits every
+    pixel once)."""
     import numpy as np
+    if fused_sweep:
+        return H * W * D * 4 * 3 + H * W * 4
     y, x = np.mgrid[0:H, 0:W]
     active = np.ones((H, W), dtype=bool)
     if direction == 5 and W != H:

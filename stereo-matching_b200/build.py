@@ -49,7 +49,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     def compile_one(job):
         src, obj = job
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+        # e.g. STM_NVCC_EXTRA="-DSTM_VSWEEP_DEBUG" (with --force) builds the developer knobs in
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("STM_NVCC_EXTRA", "").split(), "-c", str(src), "-o", str(obj)]
         r = subprocess.run(cmd, capture_output=True, text=True)
         (OBJ / (src.stem + ".ptxas.log")).write_text(r.stderr)
         if r.returncode != 0:

@@ -57,6 +57,11 @@ constexpr int kFlagStride = 32;  // unsigned per counter: counters of different 
 constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
 constexpr int kThreads = (kCols + 1) * 32;
 constexpr unsigned kSpinCap = 1u << 24;
+#ifdef STM_VSWEEP_DEBUG
+constexpr bool kDebug = true;   // STM_DEBUG_VSWEEP knobs, statistics and trace compiled in
+#else
+constexpr bool kDebug = false;
+#endif
 
 template <int DPAD>
 struct Cfg {
@@ -250,7 +255,8 @@ __device__ void importer_warp(unsigned char *smem, const Params &P, int ncols, i
     return __all_sync(FULL, ok) != 0;
   };
 
-  const bool poll = !(P.dbg & 1), stats = (P.dbg & 8) != 0;
+  const bool poll = !kDebug || !(P.dbg & 1), stats = kDebug && (P.dbg & 8) != 0;
+  const bool tracing = kDebug && (P.dbg & 16) != 0;
   unsigned long long st_polls = 0, st_ready = 0, st_credit = 0, st_rtt = 0;
   // The slots that export (0, 1) have prefetches in flight and were measured to wait ~6 us for
   // a global flag read; the importer has none, so it fetches their credit (rows the PREVIOUS
@@ -270,13 +276,13 @@ __device__ void importer_warp(unsigned char *smem, const Params &P, int ncols, i
         const int rr = r & (kR - 1);
         if (lane == 0) st_flag_s(xcred_dst, cred);
         cred = ld_relaxed_g(xcred_src);
-        long long c0 = (stats || (P.dbg & 16)) ? clock64() : 0;
+        long long c0 = (stats || tracing) ? clock64() : 0;
         if (r >= kR && poll) {  // the readers of ring row r-kR are done with it
           const unsigned par = (unsigned)(((r >> 2) - 1) & 1);
           mbar_wait(bar_empty(bars, ncols, rr), par);
           mbar_wait(bar_empty(bars, ncols + 1, rr), par);
         }
-        long long c1 = (stats || (P.dbg & 16)) ? clock64() : 0;
+        long long c1 = (stats || tracing) ? clock64() : 0;
         unsigned tries = 0;
         while (poll && !ready(buf[i], r)) {
           if (++tries > kSpinCap) __trap();
@@ -298,7 +304,7 @@ __device__ void importer_warp(unsigned char *smem, const Params &P, int ncols, i
         }
         mbar_arrive(bar_full(bars, ncols, rr));
         mbar_arrive(bar_full(bars, ncols + 1, rr));
-        if ((P.dbg & 16) && c == kTraceCta && lane == 0 && r >= kTraceRow0 && r < kTraceRow0 + kTraceRows) {
+        if (tracing && c == kTraceCta && lane == 0 && r >= kTraceRow0 && r < kTraceRow0 + kTraceRows) {
           g_trace[15][r - kTraceRow0][0] = c1; g_trace[15][r - kTraceRow0][1] = clock64();
         }
         __syncwarp();
@@ -338,12 +344,13 @@ __device__ __forceinline__ void add_weighted(LaneVec<NV, VW> &o, const LaneVec<N
   }
 }
 
-template <int NV, int VW>
+template <int NV, int VW, bool UP, bool WTA>
 __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int base, int j, int lane) {
   constexpr int DPAD = NV * 32 * VW;
   using C = Cfg<DPAD>;
   constexpr int PF = C::PF;
-  const int H = P.H, W = P.W, D = P.D, up = P.up;
+  const int H = P.H, W = P.W, D = P.D;
+  constexpr bool up = UP;
   const float p1 = P.p1, p2 = P.p2;
   const LaneCtx cx = lv_ctx<NV, VW>(lane, P.min_limit);
   const int lane_off = lane * VW;
@@ -354,11 +361,11 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   float *ringB = reinterpret_cast<float *>(smem + C::kRingBOff) + (size_t)j * kR * DPAD + lane_off;
   float *ringC = reinterpret_cast<float *>(smem + C::kRingCOff) + (size_t)j * kR * DPAD + lane_off;
   float *pf = reinterpret_cast<float *>(smem + C::kPfOff) + (size_t)j * PF * 2 * DPAD + lane_off;
-  // lanes take one of four intensity roles (lane & 3): 1, 2, 3 = the pixel behind at x-1, x, x+1
-  // (directions A, B, C); role 0 repeats role 2.  Same role, same value: the copies may collide.
-  const int role = lane & 3;
-  const int dxp = role == 0 ? 0 : role - 2;
-  float *pfi = reinterpret_cast<float *>(smem + C::kPfiOff) + j * PF * 8 + role * 2;
+  // lanes 1, 2, 3 own the intensity pair of direction A, B, C (the pixel behind at x-1, x, x+1):
+  // each copies, reads back and divides for its own direction only; the others idle along
+  const bool irole = lane >= 1 && lane <= 3;
+  const int dxp = lane - 2;
+  float *pfi = reinterpret_cast<float *>(smem + C::kPfiOff) + j * PF * 8 + (irole ? lane : 1) * 2;
 
   const long long rowstep = up ? -(long long)W : (long long)W;
   int x = base + j, y = up ? H - 1 : 0;
@@ -372,7 +379,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   // row ft: cost, sum and intensities into ring entry `e`; always exactly one commit group.
   // Past the last row the last row is fetched again (never used).
   auto issue = [&](int e) {
-    const float *cs = crow + (long long)fx * D, *ss = srow + (long long)fx * D;
+    const float *cs = crow + fx * D, *ss = srow + fx * D;
     float *dc = pf + e * 2 * DPAD;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
@@ -382,10 +389,12 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
         cp_async<VW * 4>(dc + DPAD + off, ss + off);
       }
     }
-    int pc = fx + dxp;
-    pc = pc < 0 ? 0 : (pc > W - 1 ? W - 1 : pc);
-    cp_async<4>(pfi + e * 8, irow + fx);
-    cp_async<4>(pfi + e * 8 + 1, iprev + pc);
+    if (irole) {
+      int pc = fx + dxp;
+      pc = pc < 0 ? 0 : (pc > W - 1 ? W - 1 : pc);
+      cp_async<4>(pfi + e * 8, irow + fx);
+      cp_async<4>(pfi + e * 8 + 1, iprev + pc);
+    }
     cp_async_commit();
     if (ft + 1 < H) {
       ++ft;
@@ -401,23 +410,28 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   unsigned long long *xdst = P.xring + (size_t)blockIdx.x * kRX * 3 * DPAD + lane_off;
   float *orow = P.out + (long long)y * W * D + lane_off;
   int32_t *drow = P.disp + (long long)y * W;
-  const bool sync = !(P.dbg & 2), stats = (P.dbg & 8) != 0;
-  unsigned long long st_dep = 0, st_cred = 0, st_g = 0, st_gn = 0;
-  const long long st_begin = clock64();
-  const bool store_vol = P.store_vol != 0, emit_wta = P.emit_wta != 0, defect = P.defect != 0;
+  const bool sync = !kDebug || !(P.dbg & 2), stats = kDebug && (P.dbg & 8) != 0;
+  unsigned long long st_dep = 0, st_cred = 0, st_g = 0, st_gn = 0, st_mem = 0;
+  const long long st_begin = kDebug ? clock64() : 0;
+  const bool store_vol = !WTA || P.store_vol != 0, defect = UP && P.defect != 0;
+  constexpr bool emit_wta = WTA;
   int e = 0;
 
   // penalties of the row about to be processed, computed one row ahead (off the hand-off path)
   float pa = 0.f, pb = 0.f, pc = 0.f;
 
-  const bool trace = (P.dbg & 16) && blockIdx.x == kTraceCta && lane == 0;
+  const bool trace = kDebug && (P.dbg & 16) && blockIdx.x == kTraceCta && lane == 0;
   auto mark = [&](int t, int ev) {
     if (trace && t >= kTraceRow0 && t < kTraceRow0 + kTraceRows) g_trace[j][t - kTraceRow0][ev] = clock64();
   };
 
   auto row = [&](auto first_tag, int t) {
     constexpr bool FIRST = decltype(first_tag)::value;
-    cp_async_wait<PF - 2>();  // rows t and t+1 have landed
+    {
+      const long long c0 = stats ? clock64() : 0;
+      cp_async_wait<PF - 2>();  // rows t and t+1 have landed
+      if (stats) st_mem += clock64() - c0;
+    }
     LaneVec<NV, VW> c, o;
     lv_lds<NV, VW>(c, pf + e * 2 * DPAD, 0);
     lv_lds<NV, VW>(o, pf + e * 2 * DPAD + DPAD, 0);
@@ -434,7 +448,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
 
     LaneVec<NV, VW> LB, LC;
     if constexpr (FIRST) {
-      LB = c; LC = c;
+      LB = c; LC = c; LA = c;
     } else {
       const int er = (t - 1) & (kR - 1);
       const unsigned parr = (unsigned)(((t - 1) >> 2) & 1);
@@ -450,14 +464,18 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       lv_lds<NV, VW>(LC, ringC + 2 * kR * DPAD + er * DPAD, 0);
       mbar_arrive(bar_empty(bars, j + 1, er));
       mbar_arrive(bar_empty(bars, j + 2, er));
-      // straight-line so the two recurrences interleave; the path start is a select
+      // straight-line so the three recurrences interleave; a path start is a select
       lv_sgm_step<NV, VW>(LB, c, p1, pb, cx);
       lv_sgm_step<NV, VW>(LC, c, p1, pc, cx);
-      const bool startC = x == W - 1;
+      lv_sgm_step<NV, VW>(LA, c, p1, pa, cx);
+      const bool startC = x == W - 1, startA = x == 0;
 #pragma unroll
       for (int k = 0; k < NV; ++k)
 #pragma unroll
-        for (int q = 0; q < VW; ++q) LC.v[k][q] = startC ? c.v[k][q] : LC.v[k][q];
+        for (int q = 0; q < VW; ++q) {
+          LC.v[k][q] = startC ? c.v[k][q] : LC.v[k][q];
+          LA.v[k][q] = startA ? c.v[k][q] : LA.v[k][q];
+        }
     }
 
     {  // hand the vertical and the u+2 diagonal to slots j-1, j-2 (the last row's go nowhere)
@@ -494,19 +512,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       }
     }
 
-    // Off the hand-off path, one block: the register-held diagonal (nobody's input), the next
-    // row's penalties and this row's sum / store / argmin.
-    if constexpr (FIRST) {
-      LA = c;
-    } else {
-      LaneVec<NV, VW> LAs = LA;
-      lv_sgm_step<NV, VW>(LAs, c, p1, pa, cx);
-      const bool startA = x == 0;
-#pragma unroll
-      for (int k = 0; k < NV; ++k)
-#pragma unroll
-        for (int q = 0; q < VW; ++q) LA.v[k][q] = startA ? c.v[k][q] : LAs.v[k][q];
-    }
+    // Off the hand-off path: the next row's penalties and this row's sum / store / argmin.
     {
       const float adj = sgm_p2_adjusted(p1, p2, ii.x, ii.y);
       pa = __shfl_sync(FULL, adj, 1); pb = __shfl_sync(FULL, adj, 2); pc = __shfl_sync(FULL, adj, 3);
@@ -524,7 +530,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       add_weighted<NV, VW>(o, LC, sgm_mult5(x, y, H, W));
       add_weighted<NV, VW>(o, LA, sgm_mult7(x, y, H, W));
     }
-    if (store_vol) lv_store<NV, VW, true>(o, orow + (long long)x * D, 0, D - lane_off);
+    if (store_vol) lv_store<NV, VW, true>(o, orow + x * D, 0, D - lane_off);
     if (emit_wta) lv_argmin_store<NV, VW>(o, lane, D, drow + x);
 
     mark(t, 3);
@@ -539,11 +545,11 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   cp_async_wait<0>();
   if (stats && lane == 0) {
     stat_add(8 + j, st_dep); stat_add(24 + j, st_cred); stat_add(40, st_g); stat_add(41, st_gn);
-    stat_add(42, (unsigned long long)(clock64() - st_begin)); stat_add(43, 1ull);
+    stat_add(42, (unsigned long long)(clock64() - st_begin)); stat_add(43, 1ull); stat_add(44, st_mem);
   }
 }
 
-template <int NV, int VW>
+template <int NV, int VW, bool UP, bool WTA>
 __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P) {
   extern __shared__ __align__(128) unsigned char smem[];
   using C = Cfg<NV * 32 * VW>;
@@ -561,7 +567,7 @@ __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P)
   if (threadIdx.x == 0) *reinterpret_cast<unsigned *>(smem + C::kCreditOff) = 0u;
   __syncthreads();
   if (wid == kCols) importer_warp<NV, VW>(smem, P, ncols, lane);
-  else if (wid < ncols) column_warp<NV, VW>(smem, P, ncols, base, wid, lane);
+  else if (wid < ncols) column_warp<NV, VW, UP, WTA>(smem, P, ncols, base, wid, lane);
 }
 
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
@@ -572,12 +578,18 @@ static int ctas(int W) {
   using C = Cfg<NV * 32 * VW>;
   static int cap = -1;  // per instantiation
   if (cap < 0) {
-    auto kernel = sgm_vsweep_kernel<NV, VW>;
-    int per_sm = 0;
-    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kBytes) != cudaSuccess ||
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, C::kBytes) != cudaSuccess) {
-      cudaGetLastError();
-      return 0;
+    int per_sm = 1 << 30;
+    const void *variants[3] = {(const void *)sgm_vsweep_kernel<NV, VW, false, false>,
+                               (const void *)sgm_vsweep_kernel<NV, VW, true, false>,
+                               (const void *)sgm_vsweep_kernel<NV, VW, true, true>};
+    for (const void *k : variants) {
+      int n = 0;
+      if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kBytes) != cudaSuccess ||
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, kThreads, C::kBytes) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+      }
+      per_sm = n < per_sm ? n : per_sm;
     }
     cap = per_sm * num_sms();
   }
@@ -594,7 +606,9 @@ static int run(const float *cost, const float *image, float *out, int32_t *disp,
   constexpr int DPAD = NV * 32 * VW;
   using C = Cfg<DPAD>;
   static_assert(C::kBytes <= 227 * 1024, "shared memory budget");
-  auto kernel = sgm_vsweep_kernel<NV, VW>;
+  const void *kernel = !up ? (const void *)sgm_vsweep_kernel<NV, VW, false, false>
+                           : (disp ? (const void *)sgm_vsweep_kernel<NV, VW, true, true>
+                                   : (const void *)sgm_vsweep_kernel<NV, VW, true, false>);
   const int G = ctas<NV, VW>(W);
   if (G < 1) return 1;
   Params P;
@@ -611,7 +625,7 @@ static int run(const float *cost, const float *image, float *out, int32_t *disp,
   STM_CUDA_TRY(cudaMemsetAsync(ws, 0, align256(kMaxCtas * kFlagStride * sizeof(unsigned)) +
                                           (size_t)G * kRX * 3 * DPAD * sizeof(unsigned long long), stream));
   void *args[] = {&P};
-  STM_CUDA_TRY(cudaLaunchCooperativeKernel((const void *)kernel, dim3(G), dim3(kThreads), args,
+  STM_CUDA_TRY(cudaLaunchCooperativeKernel(kernel, dim3(G), dim3(kThreads), args,
                                            (size_t)C::kBytes, stream));
   return check_launch("sgm_vsweep_kernel");
 }

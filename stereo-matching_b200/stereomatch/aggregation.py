@@ -18,26 +18,35 @@ class Semiglobal:
     min_over_all_d=False keeps the compiled CPU reference's min over d in [0, D-2]
     (SURVEY F6); True takes the min over all D like the reference CUDA kernel.
     Unlike the reference's CUDA branch, D does not have to be a power of two.
-    The default runs one kernel per direction and adds the eight directions into the output
-    in the reference's order.  fused_sweeps=True keeps the two horizontal passes and computes
-    the six directions with a vertical component as two fused sweeps (csrc/sgm_vsweep.cu):
-    four passes over the volumes instead of eight, same per-direction values, but the sum is
-    associated per sweep (2,4,6 then 3,5,7) -- within 1e-4 of the reference order, not
-    bit-identical.  Shapes the sweeps do not handle (more than 13 columns per SM, D not in
-    {<=32, 64, 128, 192, 256}) silently take the per-direction passes.  concurrent_directions=True (default) lets
-    small landscape / square volumes (<= 48 MB, latency-bound) run the eight directions at
-    the same time into per-direction buffers that are then added in the reference's order --
-    bit-identical to the sequential passes, which concurrent_directions=False forces.
+    Three schedules, same per-direction values:
+      * one kernel per direction, the eight directions added into the output in the reference's
+        order (bit-identical to the compiled CPU reference for W >= H);
+      * concurrent_directions=True (default): small landscape / square volumes (<= 48 MB,
+        latency-bound) run the eight directions at the same time into per-direction buffers that
+        are then added in the reference's order -- bit-identical to the sequential passes,
+        which concurrent_directions=False forces;
+      * fused_sweeps: the two horizontal passes, then the six directions with a vertical
+        component as two fused sweeps (csrc/sgm_vsweep.cu): four passes over the volumes instead
+        of eight.  The sum is associated per sweep (0, 1, 2+4+6, 3+5+7) -- within 1e-4 of the
+        reference order (measured 1.3e-5 at 1080p), not bit-identical.  fused_sweeps=None
+        (default) uses them for volumes above 48 MB, True always, False never (reference order).
+        Shapes the sweeps do not handle (more than 13 columns per SM, D not in {<=32, 64, 128,
+        192, 256}) take the per-direction passes.
     """
 
     def __init__(self, penalty1: float = 0.1, penalty2: float = 0.2, *,
-                 min_over_all_d: bool = False, fused_sweeps: bool = False,
+                 min_over_all_d: bool = False, fused_sweeps: Optional[bool] = None,
                  concurrent_directions: bool = True):
         self.penalty1 = penalty1
         self.penalty2 = penalty2
         self.min_over_all_d = min_over_all_d
         self.fused_sweeps = fused_sweeps
         self.concurrent_directions = concurrent_directions
+
+    def _use_fused_sweeps(self, cost_volume: torch.Tensor) -> bool:
+        if self.fused_sweeps is None:  # auto: where the passes are bandwidth-bound
+            return cost_volume.numel() * cost_volume.element_size() > (48 << 20)
+        return bool(self.fused_sweeps)
 
     def __call__(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
                  sga_volume: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -49,7 +58,7 @@ class Semiglobal:
         flags = STM_SGM_OVERWRITE | (STM_SGM_MIN_ALL_D if self.min_over_all_d else 0)
         if not self.concurrent_directions:
             flags |= STM_SGM_SEQUENTIAL
-        if self.fused_sweeps:
+        if self._use_fused_sweeps(cost_volume):
             flags |= STM_SGM_FUSED_SWEEPS
         _AggregationOps.run_semiglobal(cost_volume, left_image, self.penalty1, self.penalty2,
                                        sga_volume, flags)
@@ -74,7 +83,7 @@ class Semiglobal:
             flags |= STM_SGM_DISPARITY_ONLY
         if not self.concurrent_directions:
             flags |= STM_SGM_SEQUENTIAL
-        if self.fused_sweeps:
+        if self._use_fused_sweeps(cost_volume):
             flags |= STM_SGM_FUSED_SWEEPS
         _AggregationOps.run_semiglobal_wta(cost_volume, left_image, self.penalty1, self.penalty2,
                                            sga_volume, disparity_img, flags)

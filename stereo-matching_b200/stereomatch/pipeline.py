@@ -39,7 +39,7 @@ class Pipeline:
             if own is self._cost_volume:  # left over from a run without aggregation
                 own = None
             if (self.fuse_aggregation_and_reduce and type(self.disparity_reduce) is WinnerTakesAll
-                    and type(self.aggregation) is Semiglobal and not self.aggregation.fused_sweeps):
+                    and type(self.aggregation) is Semiglobal):
                 self._aggregation_volume, self._disparity_image = self.aggregation.aggregate_and_reduce(
                     self._cost_volume, left_image.to(self._cost_volume.device), own,
                     self._disparity_image, keep_volume=self.keep_aggregation_volume)

@@ -4,6 +4,6 @@
 TAG=${1:-vsweep}; OUT=gpurun_out; mkdir -p $OUT
 CMD="python tools/vsweep_probe.py 1080 1920 128 --reps 1"
 timeout 200 $CMD > $OUT/${TAG}_plain.log 2>&1 || { echo "plain run failed"; tail -3 $OUT/${TAG}_plain.log; exit 86; }
-timeout 800 ncu --set full --clock-control none --import-source on -k regex:sgm_vsweep -c 2 \
+timeout 800 ncu ${NCU_SET:---set full --import-source on} --clock-control none -k regex:sgm_vsweep -c 2 \
     -o $OUT/${TAG}_prof -f $CMD > $OUT/${TAG}_ncu.log 2>&1
 echo "ncu exit=$?"; tail -3 $OUT/${TAG}_ncu.log

@@ -23,7 +23,7 @@ H, W, D = a.shape
 left, right, _ = synth.random_dot_pair(H, W, D, seed=1000, scale=a.scale)
 l, r = torch.from_numpy(left).cuda(), torch.from_numpy(right).cuda()
 cost = stereomatch.cost.SSD(D)(l, r)
-plain = stereomatch.aggregation.Semiglobal(concurrent_directions=False)
+plain = stereomatch.aggregation.Semiglobal(concurrent_directions=False, fused_sweeps=False)
 fused = stereomatch.aggregation.Semiglobal(fused_sweeps=True)
 want = plain(cost, l).clone()
 got = fused(cost, l)
@@ -88,4 +88,5 @@ if int(os.environ.get("STM_DEBUG_VSWEEP", "0")) & 8:
         "slot_dep_wait_us_per_row": [round(v[8 + j] / (2 * H) / ghz / 1e3 / max(1, 148), 4) for j in range(13)],
         "slot_credit_wait_us_per_row": [round(v[24 + j] / (2 * H) / ghz / 1e3 / 148, 4) for j in range(13)],
         "xcons_wait_us_per_call": v[40] / max(v[41], 1) / ghz / 1e3, "xcons_calls": v[41],
+        "cp_async_wait_us_per_row": v[44] / max(v[43], 1) / H / ghz / 1e3,
         "warp_total_us": v[42] / max(v[43], 1) / ghz / 1e3}))
