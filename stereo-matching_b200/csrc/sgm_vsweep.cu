@@ -52,7 +52,7 @@ constexpr int kRX = 16;        // rows in the CTA->CTA ring
 #define STM_VSWEEP_PF 5
 #endif
 constexpr int kPfSmall = STM_VSWEEP_PF;
-constexpr int kLook = 4;       // rows of that ring the importer keeps loads in flight for
+constexpr int kLookMax = 4;       // rows of that ring the importer keeps loads in flight for
 constexpr int kFlagStride = 32;  // unsigned per counter: counters of different CTAs never share a line
 constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
 constexpr int kThreads = (kCols + 1) * 32;
@@ -240,6 +240,8 @@ __device__ void importer_warp(unsigned char *smem, const Params &P, int ncols, i
   float *dst[3] = {ringB + (size_t)ncols * kR * DPAD, ringC + (size_t)ncols * kR * DPAD,
                    ringC + (size_t)(ncols + 1) * kR * DPAD};
 
+  // rows of (value, tag) words in flight, bounded by registers (3 vectors x NE words per lane each)
+  constexpr int kLook = NE <= 4 ? kLookMax : (NE <= 6 ? 2 : 1);
   unsigned long long buf[kLook][3][NE];
   auto load = [&](unsigned long long (&w)[3][NE], int row) {
     const unsigned long long *s = src + (size_t)(row & (kRX - 1)) * 3 * DPAD;
