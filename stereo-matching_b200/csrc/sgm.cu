@@ -571,6 +571,7 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
 // sgm_vsweep.cu
 size_t sgm_vsweep_workspace_bytes(int H, int W, int D);
 bool sgm_vsweep_can_run(int H, int W, int D);
+int launch_sgm_vsweep_prepare(const float *, int, int, int, float, float, void *, cudaStream_t);
 int launch_sgm_vsweep(const float *, const float *, float *, int32_t *, int, int, int, float, float,
                       int, int, bool, void *, size_t, cudaStream_t);
 
@@ -597,6 +598,7 @@ static int sgm_fused(const float *cost, const float *image, float *out, int H, i
     if (rc) return rc;
   }
   pass_mark(2, 2, stream);
+  if ((rc = launch_sgm_vsweep_prepare(image, H, W, D, p1, p2, ws, stream))) return rc;
   rc = launch_sgm_vsweep(cost, image, out, nullptr, H, W, D, p1, p2, min_limit, 0, true, ws,
                          ws_bytes, stream);
   if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");

@@ -71,12 +71,13 @@ struct Cfg {
   static constexpr int kRingBOff = 1024;                               // [kCols+1][kR][DPAD]
   static constexpr int kRingCOff = kRingBOff + (kCols + 1) * kR * DPAD * 4;  // [kCols+2][kR][DPAD]
   static constexpr int kPfOff = kRingCOff + (kCols + 2) * kR * DPAD * 4;     // [kCols][PF][2][DPAD]
-  static constexpr int kPfiOff = kPfOff + kCols * PF * 2 * DPAD * 4;         // [kCols][PF][8]
-  static constexpr int kBytes = kPfiOff + kCols * PF * 8 * 4;
+  static constexpr int kPfiOff = kPfOff + kCols * PF * 2 * DPAD * 4;         // [kCols][PF] float4 penalties
+  static constexpr int kBytes = kPfiOff + kCols * PF * 16;
 };
 
 struct Params {
-  const float *cost, *image;
+  const float *cost;
+  const float4 *pen;          // [H][W] adaptive penalties (A, B, C, -) of this sweep, see sgm_vsweep_penalties
   float *out;
   int32_t *disp;
   unsigned long long *xring;  // [G][kRX][3][DPAD] (value, tag) words
@@ -353,7 +354,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   constexpr int PF = C::PF;
   const int H = P.H, W = P.W, D = P.D;
   constexpr bool up = UP;
-  const float p1 = P.p1, p2 = P.p2;
+  const float p1 = P.p1;
   const LaneCtx cx = lv_ctx<NV, VW>(lane, P.min_limit);
   const int lane_off = lane * VW;
   // shared memory, all pre-offset by this slot and lane
@@ -363,22 +364,18 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   float *ringB = reinterpret_cast<float *>(smem + C::kRingBOff) + (size_t)j * kR * DPAD + lane_off;
   float *ringC = reinterpret_cast<float *>(smem + C::kRingCOff) + (size_t)j * kR * DPAD + lane_off;
   float *pf = reinterpret_cast<float *>(smem + C::kPfOff) + (size_t)j * PF * 2 * DPAD + lane_off;
-  // lanes 1, 2, 3 own the intensity pair of direction A, B, C (the pixel behind at x-1, x, x+1):
-  // each copies, reads back and divides for its own direction only; the others idle along
-  const bool irole = lane >= 1 && lane <= 3;
-  const int dxp = lane - 2;
-  float *pfi = reinterpret_cast<float *>(smem + C::kPfiOff) + j * PF * 8 + (irole ? lane : 1) * 2;
+  float4 *pfi = reinterpret_cast<float4 *>(smem + C::kPfiOff) + j * PF;  // lane 0 copies, all read
 
   const long long rowstep = up ? -(long long)W : (long long)W;
   int x = base + j, y = up ? H - 1 : 0;
   // fetch side: row pointers (lane offset included) + column
   const float *crow = P.cost + (long long)y * W * D + lane_off;
   const float *srow = P.out + (long long)y * W * D + lane_off;
-  const float *irow = P.image + (long long)y * W, *iprev = irow;
+  const float4 *prow = P.pen + (long long)y * W;
   const long long rowstep_d = rowstep * D;
   int fx = x, ft = 0;
 
-  // row ft: cost, sum and intensities into ring entry `e`; always exactly one commit group.
+  // row ft: cost, sum and penalties into ring entry `e`; always exactly one commit group.
   // Past the last row the last row is fetched again (never used).
   auto issue = [&](int e) {
     const float *cs = crow + fx * D, *ss = srow + fx * D;
@@ -391,16 +388,11 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
         cp_async<VW * 4>(dc + DPAD + off, ss + off);
       }
     }
-    if (irole) {
-      int pc = fx + dxp;
-      pc = pc < 0 ? 0 : (pc > W - 1 ? W - 1 : pc);
-      cp_async<4>(pfi + e * 8, irow + fx);
-      cp_async<4>(pfi + e * 8 + 1, iprev + pc);
-    }
+    if (lane == 0) cp_async<16>(reinterpret_cast<float *>(pfi + e), reinterpret_cast<const float *>(prow + fx));
     cp_async_commit();
     if (ft + 1 < H) {
       ++ft;
-      iprev = irow; irow += rowstep; crow += rowstep_d; srow += rowstep_d;
+      prow += rowstep; crow += rowstep_d; srow += rowstep_d;
       fx = fx + 1 == W ? 0 : fx + 1;
     }
   };
@@ -443,7 +435,8 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
         if (k * 32 + lane >= D) { c.v[k][0] = CUDART_INF_F; o.v[k][0] = 0.f; }
     }
     const int en = e + 1 == PF ? 0 : e + 1;
-    const float2 ii = *reinterpret_cast<const float2 *>(pfi + en * 8);  // row t+1
+    __syncwarp();                  // lane 0's penalty copy of row t+1 is visible to the warp
+    const float4 pn = pfi[en];     // penalties of row t+1
     asm volatile("" ::: "memory");
     issue(e);  // refill this entry with row t + PF
     e = en;
@@ -514,11 +507,8 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       }
     }
 
-    // Off the hand-off path: the next row's penalties and this row's sum / store / argmin.
-    {
-      const float adj = sgm_p2_adjusted(p1, p2, ii.x, ii.y);
-      pa = __shfl_sync(FULL, adj, 1); pb = __shfl_sync(FULL, adj, 2); pc = __shfl_sync(FULL, adj, 3);
-    }
+    // Off the hand-off path: this row's sum / store / argmin.
+    pa = pn.x; pb = pn.y; pc = pn.z;
 
     // sum in the reference's direction order: down 2, 4, 6 = B, A, C; up 3, 5, 7 = B, C, A
     add_weighted<NV, VW>(o, LB, 1);
@@ -574,6 +564,35 @@ __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P)
 
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
 
+// Adaptive penalties max(P1, P2/|dI|) (reference src/semiglobal.cpp:134-138) of both sweeps, once
+// per call instead of a division and three shuffles per pixel inside the sweep: pen[up][y][x] =
+// (A, B, C, 0) for the pixel behind (x, y) at x-1, x, x+1 in row y-1 (down) / y+1 (up).  Entries
+// whose predecessor lies outside the image are never used (the path starts there).
+__global__ void sgm_vsweep_penalties(const float *__restrict__ image, float4 *__restrict__ pen,
+                                     int H, int W, float p1, float p2) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H * W) return;
+  const int y = i / W, x = i - y * W;
+  const float v = image[i];
+  const int xl = x > 0 ? x - 1 : x, xr = x < W - 1 ? x + 1 : x;
+#pragma unroll
+  for (int up = 0; up < 2; ++up) {
+    const int yp = up ? y + 1 : y - 1;
+    float4 r = make_float4(p1, p1, p1, 0.f);
+    if (yp >= 0 && yp < H) {
+      const float *q = image + (size_t)yp * W;
+      r.x = sgm_p2_adjusted(p1, p2, v, q[xl]);
+      r.y = sgm_p2_adjusted(p1, p2, v, q[x]);
+      r.z = sgm_p2_adjusted(p1, p2, v, q[xr]);
+    }
+    pen[(size_t)up * H * W + i] = r;
+  }
+}
+static size_t flags_and_rings_bytes(size_t dpad) {
+  return align256(kMaxCtas * kFlagStride * sizeof(unsigned)) +
+         align256((size_t)kMaxCtas * kRX * 3 * dpad * sizeof(unsigned long long));
+}
+
 // CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.
 template <int NV, int VW>
 static int ctas(int W) {
@@ -614,7 +633,8 @@ static int run(const float *cost, const float *image, float *out, int32_t *disp,
   const int G = ctas<NV, VW>(W);
   if (G < 1) return 1;
   Params P;
-  P.cost = cost; P.image = image; P.out = out; P.disp = disp;
+  P.cost = cost; P.out = out; P.disp = disp;
+  P.pen = reinterpret_cast<const float4 *>(ws + flags_and_rings_bytes(DPAD)) + (up ? (size_t)H * W : 0);
   P.xcons = reinterpret_cast<unsigned *>(ws);
   P.xring = reinterpret_cast<unsigned long long *>(ws + align256(kMaxCtas * kFlagStride * sizeof(unsigned)));
   P.H = H; P.W = W; P.D = D; P.G = G; P.q = W / G; P.r = W % G;
@@ -650,12 +670,22 @@ static bool vsweep_lane_map(int D) {
   return (m.VW == 4 && m.NV <= 2) || (m.VW == 2 && (m.NV == 1 || m.NV == 3)) || (m.VW == 1 && m.NV == 1);
 }
 
+// [imported-row counters][CTA->CTA rings][penalties of both sweeps]
 size_t sgm_vsweep_workspace_bytes(int H, int W, int D) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return 0;
   const LaneMap m = pick_lane_map(D);
-  const size_t dpad = (size_t)m.NV * 32 * m.VW;
-  return vsweep::align256(vsweep::kMaxCtas * vsweep::kFlagStride * sizeof(unsigned)) +
-         (size_t)vsweep::kMaxCtas * vsweep::kRX * 3 * dpad * sizeof(unsigned long long);
+  return vsweep::flags_and_rings_bytes((size_t)m.NV * 32 * m.VW) + (size_t)2 * H * W * sizeof(float4);
+}
+
+// Once per aggregation, before the two sweeps: the adaptive penalties of both (stream order).
+int launch_sgm_vsweep_prepare(const float *image, int H, int W, int D, float p1, float p2,
+                              void *workspace, cudaStream_t stream) {
+  const LaneMap m = pick_lane_map(D);
+  float4 *pen = reinterpret_cast<float4 *>(static_cast<char *>(workspace) +
+                                           vsweep::flags_and_rings_bytes((size_t)m.NV * 32 * m.VW));
+  const int n = H * W;
+  vsweep::sgm_vsweep_penalties<<<(n + 255) / 256, 256, 0, stream>>>(image, pen, H, W, p1, p2);
+  return check_launch("sgm_vsweep_penalties");
 }
 
 // Whether launch_sgm_vsweep will take this shape on the current device.

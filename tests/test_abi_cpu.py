@@ -45,7 +45,9 @@ def test_workspace_query_is_pure():
         # csrc/sgm_vsweep.cu (192 imported-row counters of 128 B + 192 CTA->CTA rings of
         # 16 rows x 3 vectors of 8-byte (value, tag) words; only for the lane maps it handles)
         direction = min(H, W) * dpad * 4
-        sweeps = 24576 + 192 * 16 * 3 * dpad * 8 if (H >= 2 and W >= 2 and dpad in (32, 64, 128, 192, 256)) else 0
+        # + the adaptive penalties of both sweeps, one float4 per pixel each
+        sweeps = (24576 + 192 * 16 * 3 * dpad * 8 + 2 * H * W * 16
+                  if (H >= 2 and W >= 2 and dpad in (32, 64, 128, 192, 256)) else 0)
         return max(direction, sweeps)
 
     assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == expect(1080, 1920, 128)
