@@ -82,7 +82,7 @@ struct Params {
   int32_t *disp;
   unsigned long long *xring;  // [G][kRX][3][DPAD] (value, tag) words
   unsigned *xcons;            // [G][kFlagStride] rows imported so far by CTA c (one 128-byte line each)
-  int H, W, D, G, q, r;       // units (slots, or pairs of slots) = q*G + r: CTAs [0, r) own q+1, the others q
+  int H, W, D, G, q, r;       // W = q*G + r: CTAs [0, r) own q+1 slots, the others q
   int up;                     // 0: directions 2,4,6 top to bottom; 1: 3,5,7 bottom to top
   int store_vol, emit_wta, defect, min_limit;
   int dbg;  // developer knob STM_DEBUG_VSWEEP: 1 = importer does not poll, 2 = slots do not wait (wrong results)
@@ -240,7 +240,7 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 // ---- importer: next CTA's slots 0 and 1 -> virtual slots ncols, ncols+1 ----------------------
-template <int NV, int VW, int R, int LOOK, bool PAIRS = false>
+template <int NV, int VW, int R, int LOOK>
 __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, unsigned *xcred_dst,
                               const Params &P, int ncols, int lane) {
   constexpr int DPAD = NV * 32 * VW, NE = NV * VW;
@@ -249,16 +249,8 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
   const int c = blockIdx.x;
   const int nb = c + 1 == P.G ? 0 : c + 1;
   const unsigned long long *src = P.xring + (size_t)nb * kRX * 3 * DPAD;
-  // one-warp-per-slot layout: vertical ring of slot ncols, diagonal rings of slots ncols, ncols+1;
-  // pair layout (PAIRS): ring of pair `ncols` = [row][3][DPAD] at ringB, one barrier pair
   float *dst[3] = {ringB + (size_t)ncols * R * DPAD, ringC + (size_t)ncols * R * DPAD,
                    ringC + (size_t)(ncols + 1) * R * DPAD};
-  if (PAIRS) {
-    dst[0] = ringB + (size_t)ncols * R * 3 * DPAD;
-    dst[1] = dst[0] + DPAD;
-    dst[2] = dst[0] + 2 * DPAD;
-  }
-  constexpr int kRowStride = PAIRS ? 3 * DPAD : DPAD;
 
   // rows of (value, tag) words in flight, bounded by registers (3 vectors x NE words per lane each)
   constexpr int kLook = LOOK;
@@ -303,7 +295,7 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
           // keep the exporters' credit fresh while waiting: they may be what the readers of
           // these ring rows are (transitively) waiting for -- a stale credit would deadlock
           while (!mbar_try(bar_empty<R>(bars, ncols, rr), par) ||
-                 (!PAIRS && !mbar_try(bar_empty<R>(bars, ncols + 1, rr), par))) {
+                 !mbar_try(bar_empty<R>(bars, ncols + 1, rr), par)) {
             if (lane == 0) st_flag_s(xcred_dst, cred);
             cred = ld_relaxed_g(xcred_src);
           }
@@ -326,10 +318,10 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
           for (int k = 0; k < NV; ++k)
 #pragma unroll
             for (int j = 0; j < VW; ++j) t.v[k][j] = __uint_as_float((unsigned)buf[i][v][k * VW + j]);
-          lv_sts<NV, VW>(t, dst[v] + rr * kRowStride, lane);
+          lv_sts<NV, VW>(t, dst[v] + rr * DPAD, lane);
         }
         mbar_arrive(bar_full<R>(bars, ncols, rr));
-        if (!PAIRS) mbar_arrive(bar_full<R>(bars, ncols + 1, rr));
+        mbar_arrive(bar_full<R>(bars, ncols + 1, rr));
         if (tracing && c == kTraceCta && lane == 0 && r >= kTraceRow0 && r < kTraceRow0 + kTraceRows) {
           g_trace[15][r - kTraceRow0][0] = c1; g_trace[15][r - kTraceRow0][1] = clock64();
         }
@@ -599,245 +591,6 @@ __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P)
   else if (wid < ncols) column_warp<NV, VW, UP, WTA>(smem, P, ncols, base, wid, lane);
 }
 
-// =============================================================================================
-// Two column slots per warp (lane maps with at most 4 values per lane, D <= 128, even W).
-// One slot per warp spends ~250 instructions per pixel of which ~100 are the three recurrences:
-// the rest (prefetch addressing, barriers, loop) is per warp and row, and 3.25 warps per scheduler
-// run it at ~50 % issue utilisation -- 0.93 us per row, twice the HBM time.  A warp that owns the
-// adjacent slots (2k, 2k+1) pays that overhead once for two pixels, keeps one more hand-off in
-// registers (slot 2k's vertical predecessor is slot 2k+1) and has six independent recurrences to
-// interleave.  Pair k takes three vectors per row from pair k+1 (vertical and diagonal of slot
-// 2k+2, diagonal of slot 2k+3) and hands the same three of its own to pair k-1: exactly the
-// triple the CTA->CTA ring already carries.
-namespace v3 {
-
-constexpr int kPairs = 7;  // pairs per CTA: 14 x 148 >= 1920
-constexpr int kR3 = 4;     // rows in the shared hand-off ring of a pair
-constexpr int kThreads3 = (kPairs + 1) * 32;
-
-template <int DPAD>
-struct Cfg3 {
-  static constexpr int PF = kPfSmall;                                  // prefetch ring entries (PF-1 rows ahead)
-  static constexpr int kBarOff = 0;                                    // (full, empty)[kPairs + 1][kR3]
-  static constexpr int kCreditOff = 1008;
-  static constexpr int kPenOff = 1024;                                 // float4 [kPairs][PF][2]
-  static constexpr int kRingOff = (kPenOff + kPairs * PF * 32 + 127) / 128 * 128;  // [kPairs+1][kR3][3][DPAD]
-  static constexpr int kPfOff = kRingOff + (kPairs + 1) * kR3 * 3 * DPAD * 4;       // [kPairs][PF][2][2][DPAD]
-  static constexpr int kBytes = kPfOff + kPairs * PF * 4 * DPAD * 4;
-  static_assert((kPairs + 1) * kR3 * 16 <= kCreditOff, "barriers overlap the credit word");
-};
-
-template <int NV, int VW>
-__device__ __forceinline__ void lv_select(LaneVec<NV, VW> &dst, bool take, const LaneVec<NV, VW> &a) {
-#pragma unroll
-  for (int k = 0; k < NV; ++k)
-#pragma unroll
-    for (int q = 0; q < VW; ++q) dst.v[k][q] = take ? a.v[k][q] : dst.v[k][q];
-}
-
-template <int NV, int VW, bool UP, bool WTA>
-__device__ void pair_warp(unsigned char *smem, const Params &P, int npairs, int base, int k, int lane) {
-  constexpr int DPAD = NV * 32 * VW;
-  using C = Cfg3<DPAD>;
-  constexpr int PF = C::PF;
-  const int H = P.H, W = P.W, D = P.D;
-  const float p1 = P.p1;
-  const LaneCtx cx = lv_ctx<NV, VW>(lane, P.min_limit);
-  const int lane_off = lane * VW;
-  const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
-  const unsigned *xcredit = reinterpret_cast<const unsigned *>(smem + C::kCreditOff);
-  float *ring = reinterpret_cast<float *>(smem + C::kRingOff) + (size_t)k * kR3 * 3 * DPAD + lane_off;
-  float *pf = reinterpret_cast<float *>(smem + C::kPfOff) + (size_t)k * PF * 4 * DPAD + lane_off;
-  float4 *pen = reinterpret_cast<float4 *>(smem + C::kPenOff) + k * PF * 2;
-  const bool store_vol = !WTA || P.store_vol != 0, defect = UP && P.defect != 0;
-
-  const long long rowstep = UP ? -(long long)W : (long long)W;
-  const long long rowstep_d = rowstep * D;
-  // slot a = base + 2k owns column xa, slot b = a + 1 owns xb = xa + 1 (mod W)
-  int xa = base + 2 * k, xb = xa + 1 == W ? 0 : xa + 1, y = UP ? H - 1 : 0;
-  const float *crow = P.cost + (long long)y * W * D + lane_off;
-  const float *srow = P.out + (long long)y * W * D + lane_off;
-  const float4 *prow = P.pen + (long long)y * W;
-  float *orow = P.out + (long long)y * W * D + lane_off;
-  int32_t *drow = P.disp + (long long)y * W;
-  int fxa = xa, fxb = xb, ft = 0;
-
-  // row ft of both pixels -> prefetch entry e; exactly one commit group per call
-  auto issue = [&](int e) {
-    if (ft < H) {
-      float *d0 = pf + e * 4 * DPAD;
-      const int oa = fxa * D, ob = fxb * D;
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk) {
-        const int off = kk * 32 * VW;
-        if (VW > 1 || off + lane < D) {
-          cp_async<VW * 4>(d0 + off, crow + oa + off);
-          cp_async<VW * 4>(d0 + DPAD + off, srow + oa + off);
-          cp_async<VW * 4>(d0 + 2 * DPAD + off, crow + ob + off);
-          cp_async<VW * 4>(d0 + 3 * DPAD + off, srow + ob + off);
-        }
-      }
-      if (lane < 2)
-        cp_async<16>(reinterpret_cast<float *>(pen + e * 2 + lane),
-                     reinterpret_cast<const float *>(prow + (lane == 0 ? fxa : fxb)));
-      ++ft; prow += rowstep; crow += rowstep_d; srow += rowstep_d;
-      fxa = fxa + 1 == W ? 0 : fxa + 1;
-      fxb = fxb + 1 == W ? 0 : fxb + 1;
-    }
-    cp_async_commit();
-  };
-#pragma unroll 1
-  for (int i = 0; i < PF; ++i) issue(i);
-
-  LaneVec<NV, VW> LAa, LAb, LBb;  // carried from row to row in registers
-  unsigned xc_seen = 0;
-  unsigned long long *xdst = P.xring + (size_t)blockIdx.x * kRX * 3 * DPAD + lane_off;
-  int e = 0;
-
-#pragma unroll 1
-  for (int t = 0; t < H; ++t) {
-    cp_async_wait<PF - 1>();  // row t has landed
-    LaneVec<NV, VW> ca, oa, cb, ob;
-    {
-      const float *s0 = pf + e * 4 * DPAD;
-      lv_lds<NV, VW>(ca, s0, 0);
-      lv_lds<NV, VW>(oa, s0 + DPAD, 0);
-      lv_lds<NV, VW>(cb, s0 + 2 * DPAD, 0);
-      lv_lds<NV, VW>(ob, s0 + 3 * DPAD, 0);
-    }
-    if constexpr (VW == 1) {
-#pragma unroll
-      for (int kk = 0; kk < NV; ++kk)
-        if (kk * 32 + lane >= D) {
-          ca.v[kk][0] = CUDART_INF_F; cb.v[kk][0] = CUDART_INF_F; oa.v[kk][0] = 0.f; ob.v[kk][0] = 0.f;
-        }
-    }
-    __syncwarp();  // the penalty copies of lanes 0 and 1 are visible to the warp
-    const float4 pna = pen[e * 2], pnb = pen[e * 2 + 1];
-    const int e_refill = e;
-    e = e + 1 == PF ? 0 : e + 1;
-
-    LaneVec<NV, VW> LBa, LCa, LCb;
-    if (t == 0) {
-      LBa = ca; LCa = ca; LAa = ca; LBb = cb; LCb = cb; LAb = cb;
-    } else {
-      const int er = (t - 1) & (kR3 - 1);
-      mbar_wait(bar_full<kR3>(bars, k + 1, er), (unsigned)(((t - 1) / kR3) & 1));
-      const float *rp = ring + (size_t)(kR3 + er) * 3 * DPAD;  // pair k+1, row t-1
-      LaneVec<NV, VW> Bn;
-      lv_lds<NV, VW>(Bn, rp, 0);             // vertical of slot 2k+2
-      lv_lds<NV, VW>(LCa, rp + DPAD, 0);     // diagonal of slot 2k+2
-      lv_lds<NV, VW>(LCb, rp + 2 * DPAD, 0);  // diagonal of slot 2k+3
-      mbar_arrive(bar_empty<kR3>(bars, k + 1, er));
-      LBa = LBb;  // slot a's vertical predecessor is slot b's vector of the previous row
-      LBb = Bn;
-      // six independent recurrences, straight-line; a path start is a select
-      lv_sgm_step<NV, VW>(LBa, ca, p1, pna.y, cx);
-      lv_sgm_step<NV, VW>(LBb, cb, p1, pnb.y, cx);
-      lv_sgm_step<NV, VW>(LCa, ca, p1, pna.z, cx);
-      lv_sgm_step<NV, VW>(LCb, cb, p1, pnb.z, cx);
-      lv_select<NV, VW>(LCa, xa == W - 1, ca);
-      lv_select<NV, VW>(LCb, xb == W - 1, cb);
-    }
-
-    {  // hand (vertical, diagonal) of slot a and the diagonal of slot b to pair k-1
-      const int ew = t & (kR3 - 1);
-      if (k >= 1) {
-        if (t >= kR3) mbar_wait(bar_empty<kR3>(bars, k, ew), (unsigned)(((t / kR3) - 1) & 1));
-        float *wp = ring + (size_t)ew * 3 * DPAD;
-        lv_sts<NV, VW>(LBa, wp, 0);
-        lv_sts<NV, VW>(LCa, wp + DPAD, 0);
-        lv_sts<NV, VW>(LCb, wp + 2 * DPAD, 0);
-        mbar_arrive(bar_full<kR3>(bars, k, ew));
-      } else if (t < H - 1) {  // pair 0: to the previous CTA
-        if (t >= kRX) {
-          const unsigned need_x = (unsigned)(t - kRX + 1);
-          if (xc_seen < need_x) {
-            unsigned tries = 0;
-            while ((xc_seen = ld_flag_s(xcredit)) < need_x) {
-              __nanosleep(100);
-              if (++tries > kSpinCap) __trap();
-            }
-          }
-        }
-        unsigned long long *ex = xdst + (size_t)(t & (kRX - 1)) * 3 * DPAD;
-        lv_st_ll<NV, VW>(LBa, ex, 0, (unsigned)(t + 1));
-        lv_st_ll<NV, VW>(LCa, ex + DPAD, 0, (unsigned)(t + 1));
-        lv_st_ll<NV, VW>(LCb, ex + 2 * DPAD, 0, (unsigned)(t + 1));
-      }
-    }
-
-    asm volatile("" ::: "memory");
-    issue(e_refill);  // refill the entry just consumed with row t + PF
-
-    // the register-held diagonals are nobody's input: after the hand-off
-    if (t > 0) {
-      lv_sgm_step<NV, VW>(LAa, ca, p1, pna.x, cx);
-      lv_sgm_step<NV, VW>(LAb, cb, p1, pnb.x, cx);
-      lv_select<NV, VW>(LAa, xa == 0, ca);
-      lv_select<NV, VW>(LAb, xb == 0, cb);
-    }
-
-    // sums in the reference's direction order: down 2, 4, 6 = B, A, C; up 3, 5, 7 = B, C, A
-    add_weighted<NV, VW>(oa, LBa, 1);
-    add_weighted<NV, VW>(ob, LBb, 1);
-    if (!UP) {
-      add_weighted<NV, VW>(oa, LAa, 1); add_weighted<NV, VW>(ob, LAb, 1);
-      add_weighted<NV, VW>(oa, LCa, 1); add_weighted<NV, VW>(ob, LCb, 1);
-    } else if (!defect) {
-      add_weighted<NV, VW>(oa, LCa, 1); add_weighted<NV, VW>(ob, LCb, 1);
-      add_weighted<NV, VW>(oa, LAa, 1); add_weighted<NV, VW>(ob, LAb, 1);
-    } else {
-      add_weighted<NV, VW>(oa, LCa, sgm_mult5(xa, y, H, W));
-      add_weighted<NV, VW>(ob, LCb, sgm_mult5(xb, y, H, W));
-      add_weighted<NV, VW>(oa, LAa, sgm_mult7(xa, y, H, W));
-      add_weighted<NV, VW>(ob, LAb, sgm_mult7(xb, y, H, W));
-    }
-    if (store_vol) {
-      lv_store<NV, VW, true>(oa, orow + xa * D, 0, D - lane_off);
-      lv_store<NV, VW, true>(ob, orow + xb * D, 0, D - lane_off);
-    }
-    if (WTA) {
-      lv_argmin_store<NV, VW>(oa, lane, D, drow + xa);
-      lv_argmin_store<NV, VW>(ob, lane, D, drow + xb);
-    }
-    xa = xa + 1 == W ? 0 : xa + 1;
-    xb = xb + 1 == W ? 0 : xb + 1;
-    y += UP ? -1 : 1;
-    orow += rowstep_d; drow += rowstep;
-  }
-  cp_async_wait<0>();
-}
-
-template <int NV, int VW, bool UP, bool WTA>
-__global__ void __launch_bounds__(kThreads3, 1) sgm_vsweep3_kernel(const Params P) {
-  extern __shared__ __align__(128) unsigned char smem[];
-  constexpr int DPAD = NV * 32 * VW;
-  using C = Cfg3<DPAD>;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int c = blockIdx.x;
-  // P.q, P.r count PAIRS here: W / 2 = q*G + r
-  const int npairs = P.q + (c < P.r ? 1 : 0);
-  const int base = 2 * (c * P.q + (c < P.r ? c : P.r));
-  if (threadIdx.x < (kPairs + 1) * kR3) {
-    const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
-    const int sl = threadIdx.x / kR3, e = threadIdx.x % kR3;
-    mbar_init(bar_full<kR3>(bars, sl, e), 32u);   // every lane of the writer
-    mbar_init(bar_empty<kR3>(bars, sl, e), 32u);  // every lane of the one reader (pair sl-1)
-  }
-  if (threadIdx.x == 0) *reinterpret_cast<unsigned *>(smem + C::kCreditOff) = 0u;
-  __syncthreads();
-  if (wid == kPairs) {
-    importer_core<NV, VW, kR3, (NV * VW <= 4 ? kLookMax : 2), true>(
-        (unsigned)__cvta_generic_to_shared(smem + C::kBarOff), reinterpret_cast<float *>(smem + C::kRingOff),
-        nullptr, reinterpret_cast<unsigned *>(smem + C::kCreditOff), P, npairs, lane);
-  } else if (wid < npairs) {
-    pair_warp<NV, VW, UP, WTA>(smem, P, npairs, base, wid, lane);
-  }
-}
-
-}  // namespace v3
-
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
 
 // Adaptive penalties max(P1, P2/|dI|) (reference src/semiglobal.cpp:134-138) of both sweeps, once
@@ -869,57 +622,35 @@ static size_t flags_and_rings_bytes(size_t dpad) {
          align256((size_t)kMaxCtas * kRX * 3 * dpad * sizeof(unsigned long long));
 }
 
-// The kernel of a sweep: two slots per warp (v3) where a lane holds at most 4 values (D <= 128)
-// and W is even, one slot per warp otherwise.  STM_DEBUG_VSWEEP_ONE=1 forces the latter
-// (developer knob).  A "unit" is what a warp owns: a pair of slots or one slot.
+// CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.
 template <int NV, int VW>
-struct Variant {
-  static bool pairs(int W) {
-    static const char *one = getenv("STM_DEBUG_VSWEEP_ONE");
-    return NV * VW <= 4 && W % 2 == 0 && !(one && one[0] == '1');
-  }
-  static const void *kernel(bool pr, bool up, bool wta) {
-    if constexpr (NV * VW <= 4) {
-      if (pr)
-        return !up ? (const void *)v3::sgm_vsweep3_kernel<NV, VW, false, false>
-                   : (wta ? (const void *)v3::sgm_vsweep3_kernel<NV, VW, true, true>
-                          : (const void *)v3::sgm_vsweep3_kernel<NV, VW, true, false>);
-    }
-    return !up ? (const void *)sgm_vsweep_kernel<NV, VW, false, false>
-               : (wta ? (const void *)sgm_vsweep_kernel<NV, VW, true, true>
-                      : (const void *)sgm_vsweep_kernel<NV, VW, true, false>);
-  }
-  static int smem(bool pr) { return pr ? v3::Cfg3<NV * 32 * VW>::kBytes : Cfg<NV * 32 * VW>::kBytes; }
-  static int threads(bool pr) { return pr ? v3::kThreads3 : kThreads; }
-  static int units(bool pr, int W) { return pr ? W / 2 : W; }
-  static int max_units_per_cta(bool pr) { return pr ? v3::kPairs : kCols; }
-  static int min_units_per_cta(bool pr) { return pr ? 1 : 2; }
-};
+static const void *sweep_kernel(bool up, bool wta) {
+  return !up ? (const void *)sgm_vsweep_kernel<NV, VW, false, false>
+             : (wta ? (const void *)sgm_vsweep_kernel<NV, VW, true, true>
+                    : (const void *)sgm_vsweep_kernel<NV, VW, true, false>);
+}
 
-// CTAs for an image W columns wide (all co-resident), or 0 when the sweeps cannot take it.
 template <int NV, int VW>
 static int ctas(int W) {
-  using V = Variant<NV, VW>;
-  const bool pr = V::pairs(W);
-  static int cap[2] = {-1, -1};  // per instantiation and variant
-  if (cap[pr] < 0) {
+  using C = Cfg<NV * 32 * VW>;
+  static int cap = -1;  // per instantiation
+  if (cap < 0) {
     int per_sm = 1 << 30;
     for (int v = 0; v < 3; ++v) {
-      const void *k = V::kernel(pr, v > 0, v > 1);
+      const void *k = sweep_kernel<NV, VW>(v > 0, v > 1);
       int n = 0;
-      if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, V::smem(pr)) != cudaSuccess ||
-          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, V::threads(pr), V::smem(pr)) != cudaSuccess) {
+      if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kBytes) != cudaSuccess ||
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, kThreads, C::kBytes) != cudaSuccess) {
         cudaGetLastError();
         return 0;
       }
       per_sm = n < per_sm ? n : per_sm;
     }
-    cap[pr] = per_sm * num_sms();
+    cap = per_sm * num_sms();
   }
-  const int units = V::units(pr, W);
-  int G = cap[pr] < kMaxCtas ? cap[pr] : kMaxCtas;
-  if (G > units / V::min_units_per_cta(pr)) G = units / V::min_units_per_cta(pr);
-  if (G < 1 || (units + G - 1) / G > V::max_units_per_cta(pr)) return 0;
+  int G = cap < kMaxCtas ? cap : kMaxCtas;
+  if (G > W / 2) G = W / 2;
+  if (G < 1 || (W + G - 1) / G > kCols) return 0;
   return G;
 }
 
@@ -928,20 +659,17 @@ static int run(const float *cost, const float *image, float *out, int32_t *disp,
                float p1, float p2, int min_limit, int up, bool store_vol, char *ws,
                cudaStream_t stream) {
   constexpr int DPAD = NV * 32 * VW;
-  using V = Variant<NV, VW>;
-  static_assert(Cfg<DPAD>::kBytes <= 227 * 1024, "shared memory budget");
-  static_assert(NV * VW > 4 || v3::Cfg3<DPAD>::kBytes <= 227 * 1024, "shared memory budget");
-  const bool pr = V::pairs(W);
-  const void *kernel = V::kernel(pr, up != 0, disp != nullptr);
+  using C = Cfg<DPAD>;
+  static_assert(C::kBytes <= 227 * 1024, "shared memory budget");
+  const void *kernel = sweep_kernel<NV, VW>(up != 0, disp != nullptr);
   const int G = ctas<NV, VW>(W);
   if (G < 1) return 1;
-  const int units = V::units(pr, W);
   Params P;
   P.cost = cost; P.out = out; P.disp = disp;
   P.pen = reinterpret_cast<const float4 *>(ws + flags_and_rings_bytes(DPAD)) + (up ? (size_t)H * W : 0);
   P.xcons = reinterpret_cast<unsigned *>(ws);
   P.xring = reinterpret_cast<unsigned long long *>(ws + align256(kMaxCtas * kFlagStride * sizeof(unsigned)));
-  P.H = H; P.W = W; P.D = D; P.G = G; P.q = units / G; P.r = units % G;
+  P.H = H; P.W = W; P.D = D; P.G = G; P.q = W / G; P.r = W % G;
   P.up = up; P.store_vol = store_vol ? 1 : 0; P.emit_wta = disp ? 1 : 0;
   P.defect = (up && W != H) ? 1 : 0;
   P.min_limit = min_limit; P.p1 = p1; P.p2 = p2;
@@ -951,8 +679,8 @@ static int run(const float *cost, const float *image, float *out, int32_t *disp,
   STM_CUDA_TRY(cudaMemsetAsync(ws, 0, align256(kMaxCtas * kFlagStride * sizeof(unsigned)) +
                                           (size_t)G * kRX * 3 * DPAD * sizeof(unsigned long long), stream));
   void *args[] = {&P};
-  STM_CUDA_TRY(cudaLaunchCooperativeKernel(kernel, dim3(G), dim3(V::threads(pr)), args,
-                                           (size_t)V::smem(pr), stream));
+  STM_CUDA_TRY(cudaLaunchCooperativeKernel(kernel, dim3(G), dim3(kThreads), args,
+                                           (size_t)C::kBytes, stream));
   return check_launch("sgm_vsweep_kernel");
 }
 
