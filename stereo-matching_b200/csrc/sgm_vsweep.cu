@@ -55,7 +55,7 @@ constexpr int kPfSmall = STM_VSWEEP_PF;
 constexpr int kLookMax = 4;       // rows of that ring the importer keeps loads in flight for
 constexpr int kFlagStride = 32;  // unsigned per counter: counters of different CTAs never share a line
 constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
-constexpr int kThreads = (kCols + 1) * 32;
+constexpr int kThreads = (kCols + 2) * 32;  // column slots + importer + exporter
 constexpr unsigned kSpinCap = 1u << 24;
 #ifdef STM_VSWEEP_DEBUG
 constexpr bool kDebug = true;   // STM_DEBUG_VSWEEP knobs, statistics and trace compiled in
@@ -135,8 +135,9 @@ __device__ __forceinline__ unsigned bar_full(unsigned base, int s, int e) { retu
 template <int R = kR>
 __device__ __forceinline__ unsigned bar_empty(unsigned base, int s, int e) { return base + (unsigned)((s * R + e) * 16 + 8); }
 // readers of slot s's ring rows: slot s-1 takes the vertical vector, slot s-2 the diagonal
+// and the exporter warp takes both from slots 0 and 1
 __device__ __forceinline__ int slot_readers(int s, int ncols) {
-  return ((s - 1 >= 0 && s - 1 < ncols) ? 1 : 0) + ((s - 2 >= 0 && s - 2 < ncols) ? 1 : 0);
+  return ((s - 1 >= 0 && s - 1 < ncols) ? 1 : 0) + ((s - 2 >= 0 && s - 2 < ncols) ? 1 : 0) + (s < 2 ? 1 : 0);
 }
 __device__ __forceinline__ unsigned ld_flag_s(const unsigned *p) {
   unsigned v;
@@ -357,6 +358,48 @@ __device__ void importer_warp(unsigned char *smem, const Params &P, int ncols, i
                                   reinterpret_cast<unsigned *>(smem + C::kCreditOff), P, ncols, lane);
 }
 
+// ---- exporter: slots 0 and 1 of this CTA -> the previous CTA ---------------------------------
+// A warp of its own, with no prefetch in flight: the .gpu-scope stores (and loads) of a column
+// warp were measured to take ~5 us behind its outstanding cp.async traffic, the same accesses
+// from a warp without any ~0.4 us -- and that latency is paid once per CTA on the ring.
+template <int NV, int VW>
+__device__ void exporter_warp(unsigned char *smem, const Params &P, int lane) {
+  constexpr int DPAD = NV * 32 * VW;
+  using C = Cfg<DPAD>;
+  const int nrows = P.H - 1;  // the last row's vectors have no consumer
+  const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
+  const unsigned *xcredit = reinterpret_cast<const unsigned *>(smem + C::kCreditOff);
+  const float *ringB = reinterpret_cast<const float *>(smem + C::kRingBOff);
+  const float *ringC = reinterpret_cast<const float *>(smem + C::kRingCOff);
+  unsigned long long *xdst = P.xring + (size_t)blockIdx.x * kRX * 3 * DPAD;
+  unsigned xc_seen = 0;
+#pragma unroll 1
+  for (int t = 0; t < nrows; ++t) {
+    const int e = t & (kR - 1);
+    const unsigned par = (unsigned)((t / kR) & 1);
+    mbar_wait(bar_full(bars, 0, e), par);
+    mbar_wait(bar_full(bars, 1, e), par);
+    LaneVec<NV, VW> B0, C0, C1;
+    lv_lds<NV, VW>(B0, ringB + e * DPAD, lane);
+    lv_lds<NV, VW>(C0, ringC + e * DPAD, lane);
+    lv_lds<NV, VW>(C1, ringC + (kR + e) * DPAD, lane);
+    mbar_arrive(bar_empty(bars, 0, e));
+    mbar_arrive(bar_empty(bars, 1, e));
+    if (t >= kRX) {  // the previous CTA has imported row t-kRX
+      const unsigned need_x = (unsigned)(t - kRX + 1);
+      unsigned tries = 0;
+      while (xc_seen < need_x) {
+        xc_seen = ld_flag_s(xcredit);
+        if (++tries > kSpinCap) __trap();
+      }
+    }
+    unsigned long long *ex = xdst + (size_t)(t & (kRX - 1)) * 3 * DPAD;
+    lv_st_ll<NV, VW>(B0, ex, lane, (unsigned)(t + 1));
+    lv_st_ll<NV, VW>(C0, ex + DPAD, lane, (unsigned)(t + 1));
+    lv_st_ll<NV, VW>(C1, ex + 2 * DPAD, lane, (unsigned)(t + 1));
+  }
+}
+
 // ---- one column slot ------------------------------------------------------------------------
 template <int NV, int VW>
 __device__ __forceinline__ void add_weighted(LaneVec<NV, VW> &o, const LaneVec<NV, VW> &L, int mult) {
@@ -386,8 +429,6 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   const int lane_off = lane * VW;
   // shared memory, all pre-offset by this slot and lane
   const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
-  const bool has_readers = j >= 1;
-  const unsigned *xcredit = reinterpret_cast<const unsigned *>(smem + C::kCreditOff);
   float *ringB = reinterpret_cast<float *>(smem + C::kRingBOff) + (size_t)j * kR * DPAD + lane_off;
   float *ringC = reinterpret_cast<float *>(smem + C::kRingCOff) + (size_t)j * kR * DPAD + lane_off;
   float *pf = reinterpret_cast<float *>(smem + C::kPfOff) + (size_t)j * PF * 2 * DPAD + lane_off;
@@ -427,8 +468,6 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   for (int i = 0; i < PF; ++i) issue(i);
 
   LaneVec<NV, VW> LA;
-  unsigned xc_seen = 0;
-  unsigned long long *xdst = P.xring + (size_t)blockIdx.x * kRX * 3 * DPAD + lane_off;
   float *orow = P.out + (long long)y * W * D + lane_off;
   int32_t *drow = P.disp + (long long)y * W;
   const bool sync = !kDebug || !(P.dbg & 2), stats = kDebug && (P.dbg & 8) != 0;
@@ -501,7 +540,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
 
     {  // hand the vertical and the u+2 diagonal to slots j-1, j-2 (the last row's go nowhere)
       const int ew = t & (kR - 1);
-      if (t >= kR && has_readers && sync) {  // ring row t-kR has been read by slots j-1, j-2
+      if (t >= kR && sync) {  // ring row t-kR has been read by slots j-1, j-2
         const long long c0 = stats ? clock64() : 0;
         mbar_wait(bar_empty(bars, j, ew), (unsigned)(((t >> 2) - 1) & 1));
         if (stats) st_cred += clock64() - c0;
@@ -510,27 +549,6 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       lv_sts<NV, VW>(LC, ringC + ew * DPAD, 0);
       mbar_arrive(bar_full(bars, j, ew));
       mark(t, 2);
-      if (j < 2 && t < H - 1) {  // and to the previous CTA
-        if (t >= kRX) {
-          const unsigned need_x = (unsigned)(t - kRX + 1);
-          if (xc_seen < need_x && sync) {
-            const long long c0 = stats ? clock64() : 0;
-            unsigned tries = 0;
-            while ((xc_seen = ld_flag_s(xcredit)) < need_x) {
-              __nanosleep(100);
-              if (++tries > kSpinCap) __trap();
-            }
-            if (stats) { st_g += clock64() - c0; st_gn += 1; }
-          }
-        }
-        unsigned long long *ex = xdst + (size_t)(t & (kRX - 1)) * 3 * DPAD;
-        if (j == 0) {
-          lv_st_ll<NV, VW>(LB, ex, 0, (unsigned)(t + 1));
-          lv_st_ll<NV, VW>(LC, ex + DPAD, 0, (unsigned)(t + 1));
-        } else {
-          lv_st_ll<NV, VW>(LC, ex + 2 * DPAD, 0, (unsigned)(t + 1));
-        }
-      }
     }
 
     // Off the hand-off path: refill the prefetch entry just consumed with row t + PF, then this
@@ -588,6 +606,7 @@ __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P)
   if (threadIdx.x == 0) *reinterpret_cast<unsigned *>(smem + C::kCreditOff) = 0u;
   __syncthreads();
   if (wid == kCols) importer_warp<NV, VW>(smem, P, ncols, lane);
+  else if (wid == kCols + 1) exporter_warp<NV, VW>(smem, P, lane);
   else if (wid < ncols) column_warp<NV, VW, UP, WTA>(smem, P, ncols, base, wid, lane);
 }
 

@@ -11,6 +11,6 @@ timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_d
     --clock-control none -c 200 --csv --log-file $OUT/${TAG}_dram.csv $CMD > $OUT/${TAG}_ncu1.log 2>&1
 echo "ncu dram pass exit=$?"
 timeout 300 $CMD > $OUT/${TAG}_plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:sgm_path_kernel -s 9 -c 2 \
-    -f -o $OUT/${TAG}_sgm_path_full $CMD > $OUT/${TAG}_ncu2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:sgm_vsweep_kernel -c 2 \
+    -f -o $OUT/${TAG}_sgm_vsweep_full $CMD > $OUT/${TAG}_ncu2.log 2>&1
 echo "ncu full pass exit=$?"; tail -3 $OUT/${TAG}_ncu2.log
