@@ -43,11 +43,16 @@ extern "C" {
                                 instead of k in [0, D-2] (compiled CPU reference,
                                 src/bordered_buffer.hpp:26-27) */
 #define STM_SGM_OVERWRITE 2u /* out = sum (skip the caller's zero fill) instead of out += sum */
-#define STM_SGM_FUSED_SWEEPS 4u /* EXPERIMENTAL: two fused raster sweeps (csrc/sgm_wave.cu) instead of
-                                   one kernel per direction.  Moves ~20 instead of ~92 B/pix-disp of
-                                   HBM traffic and passes the same parity tests, but is latency-bound
-                                   and currently ~5x SLOWER (profiles/r01_v3_fused_sweeps.md).  fp32
-                                   sums associate differently (same values within a few ulp). */
+#define STM_SGM_FUSED_SWEEPS 4u /* the two horizontal directions as passes of their own, then the six
+                                   directions with a vertical component as two fused sweeps
+                                   (csrc/sgm_vsweep.cu): four passes over the volumes instead of
+                                   eight (11.6 instead of 21.3 GB of DRAM traffic at 1080p D=128).
+                                   Same per-direction vectors; the sum is associated per sweep
+                                   (0, 1, 2+4+6, 3+5+7) and the corner up-diagonals add mult*L in one
+                                   fused multiply-add: within 1e-4 of the reference order, not
+                                   bit-identical.  Cooperative launch, one CTA per SM.  Shapes the
+                                   sweeps do not take (W > 13 x #SMs, D not in {<= 32, 64, 128, 192,
+                                   256}, unaligned pointers) run the per-direction passes. */
 #define STM_SGM_DISPARITY_ONLY 8u /* stm_sgm_wta_f32 only: `out` is scratch.  The last pass reduces
                                      the finished sums to the disparity map without writing them
                                      back (4 B/pix-disp less HBM traffic); on return `out` holds
@@ -86,8 +91,9 @@ int stm_birchfield_f32(const float *left, const float *right, float *cost, int H
  * Aggregates over the reference path set (8 directions, including its stored-end quirk)
  * and ACCUMULATES into `out` unless STM_SGM_OVERWRITE.  `workspace` must hold
  * stm_sgm_workspace_bytes(H, W, D) bytes of device memory (may be NULL if that is 0): one
- * path's worth of vectors for the corner-diagonal replay, the rings of the experimental fused
- * sweeps and, for landscape / square volumes of at most 48 MB, eight volume-sized buffers (those
+ * path's worth of vectors for the corner-diagonal replay, the CTA-to-CTA rings and the per-pixel
+ * penalties of the fused sweeps and, for landscape / square volumes of at most 48 MB, eight
+ * volume-sized buffers (those
  * shapes run the eight directions concurrently on library-owned streams that are forked from and
  * joined to `stream`; see STM_SGM_SEQUENTIAL).  The query is a pure function of the shape. */
 size_t stm_sgm_workspace_bytes(int H, int W, int D);
@@ -103,16 +109,18 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
  * equals stm_sgm_f32's result up to fp32 association (a few ulp).  `out` is still written
  * unless STM_SGM_DISPARITY_ONLY is given (what Pipeline.estimate uses: it never hands the
  * aggregated volume to its caller).
- * flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY | STM_SGM_SEQUENTIAL. */
+ * flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY | STM_SGM_SEQUENTIAL |
+ * STM_SGM_FUSED_SWEEPS (then the up sweep takes the argmin; no direction swap is needed). */
 int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *disparity, int H,
                     int W, int D, float penalty1, float penalty2, unsigned flags, void *workspace,
                     size_t workspace_bytes, void *stream);
 
 /* Measurement API (new; bench.py's per-pass roofline lines).  With timing enabled, every
  * stm_sgm_f32 / stm_sgm_wta_f32 call records CUDA events on its stream around each of the
- * eight direction passes (a pass = the direction's kernel plus its corner-diagonal replay, see
- * SURVEY.md F5).  stm_sgm_last_pass_ms waits for the last call's final event and returns the
- * number of passes (8; 0 if no call was timed), filling ms[i] and directions[i] in launch
+ * passes (a pass = one direction's kernel plus its corner-diagonal replay, see SURVEY.md F5, or
+ * one fused sweep: directions[] then holds 2 for 2+4+6 and 3 for 3+5+7).  stm_sgm_last_pass_ms
+ * waits for the last call's final event and returns the number of passes (8, or 4 with
+ * STM_SGM_FUSED_SWEEPS; 0 if no call was timed), filling ms[i] and directions[i] in launch
  * order.  Process-wide state, not thread-safe: a measurement switch, not a product feature. */
 int stm_sgm_pass_timing(int enable);
 int stm_sgm_last_pass_ms(float *ms, int *directions, int capacity);
