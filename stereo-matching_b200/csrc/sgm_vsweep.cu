@@ -19,23 +19,30 @@
 // re-enters on the left, where the register-held diagonal starts a new path (L = C); the
 // u+2 diagonal starts a new path at x = W-1.  All W slots do exactly H steps.
 //
-// CTA c owns `ncols` (2..13) consecutive slots, one warp each, plus one importer warp.
-// Inside a CTA slots publish their vertical / diagonal vectors to 4-row rings in shared
-// memory behind relaxed progress flags (no fence: see sgm_wave history, a CTA-scope release
-// compiles to MEMBAR.ALL.CTA and waits for the warp's prefetches).  Between CTAs, slots 0 and
-// 1 write (value, row tag) pairs as single 8-byte words into an L2-resident ring (the tag
-// travels with the data: no fence, no separate flag) and the consumer CTA's importer warp
-// polls them one row ahead and feeds two virtual slots of the shared rings, so compute warps
-// see one interface.  Credits flow back through the progress flags (shared) and a per-CTA
-// imported-rows counter (global).  All CTAs must be co-resident: cooperative launch.
+// CTA c owns `ncols` (2..13) consecutive slots, one warp each, plus an importer and an exporter
+// warp.  Inside a CTA a slot publishes its vertical / u+2-diagonal vectors to 4-row rings in
+// shared memory behind a (full, empty) mbarrier pair per slot and ring row; a waiting warp is
+// suspended by try_wait (spinning neighbours took the issue slots of the warp everybody waits
+// for).  Between CTAs the exporter warp writes slots 0 and 1's vectors as (value, row tag) pairs
+// in single 8-byte words into an L2-resident ring (the tag travels with the data: no fence, no
+// separate flag) and the previous CTA's importer warp polls them a few rows ahead and feeds two
+// virtual slots of the shared rings, so column warps see one interface.  Credits flow back
+// through the `empty` barriers and a per-CTA imported-rows counter that the importer mirrors
+// into shared memory.  Importer and exporter are warps of their own because a .gpu-scope load or
+// store issued by a warp with cp.async prefetches in flight was measured at 4-6 us instead of
+// 0.35 us.  All CTAs must be co-resident: cooperative launch.
 //
-// Cost and sum vectors of the next PF rows are in flight as per-lane cp.async copies into a
-// private shared-memory ring (a lane only reads back bytes it copied itself: no barrier).
+// Cost and sum vectors of the next rows are in flight as per-lane cp.async copies into a
+// private shared-memory ring (a lane only reads back bytes it copied itself: no barrier).  The
+// adaptive penalties max(P1, P2/|dI|) of both sweeps come from a pre-kernel (one float4 per
+// pixel and sweep) and are fetched with the row.
 //
 // Values: same recurrences and same per-direction vectors as sgm.cu; the sum is associated
 // (((S + v) + d1) + d2) per sweep instead of the reference's 0..7 order, and the corner
 // up-diagonals add mult*L in one fused multiply-add instead of mult additions
-// -- within the 1e-4 bar, not bit-identical (STM_SGM_FUSED_SWEEPS is opt-in for that reason).
+// -- within the 1e-4 bar (measured 1.3e-5), not bit-identical: callers that want the reference
+// order bit for bit leave STM_SGM_FUSED_SWEEPS off.  Measurements and the designs that were
+// tried and removed: profiles/r01_v26_fused_vertical_sweeps.md, DESIGN.md 3.4.
 #include "lanevec.cuh"
 #include <cstdlib>
 #include <type_traits>
