@@ -63,7 +63,26 @@ constexpr int kLookMax = 4;       // rows of that ring the importer keeps loads 
 constexpr int kFlagStride = 32;  // unsigned per counter: counters of different CTAs never share a line
 constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
 constexpr int kThreads = (kCols + 2) * 32;  // column slots + importer + exporter
-constexpr unsigned kSpinCap = 1u << 24;
+// A polling loop that makes no progress for kSpinSeconds of wall clock traps instead of hanging
+// the GPU (a bug, not a slow neighbour: profilers and time-slicing can stall a CTA for a long
+// time, so the guard is on %globaltimer, looked at every 4096 polls, not on an iteration count).
+constexpr unsigned long long kSpinSeconds = 60;
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+struct SpinGuard {
+  unsigned polls = 0;
+  unsigned long long t0 = 0;
+  __device__ __forceinline__ void poll() {
+    if ((++polls & 4095u) == 0) {
+      const unsigned long long now = global_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kSpinSeconds * 1000000000ull) __trap();
+    }
+  }
+};
 #ifdef STM_VSWEEP_DEBUG
 constexpr bool kDebug = true;   // STM_DEBUG_VSWEEP knobs, statistics and trace compiled in
 #else
@@ -310,8 +329,10 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
         }
         long long c1 = (stats || tracing) ? clock64() : 0;
         unsigned tries = 0;
+        SpinGuard guard;
         while (poll && !ready(buf[i], r)) {
-          if (++tries > kSpinCap) __trap();
+          ++tries;
+          guard.poll();
           const long long r0 = stats ? clock64() : 0;
           if (lane == 0) st_flag_s(xcred_dst, cred);
           cred = ld_relaxed_g(xcred_src);
@@ -341,10 +362,9 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
     }
   }
   // the exporters' last credit: the previous CTA has imported row H-2-kRX
-  for (unsigned tries = 0;; ++tries) {
+  for (SpinGuard guard;; guard.poll()) {
     if (lane == 0) st_flag_s(xcred_dst, cred);
     if ((int)cred >= nrows - kRX) break;
-    if (tries > kSpinCap) __trap();
     cred = ld_relaxed_g(xcred_src);
   }
   if (stats && lane == 0) {
@@ -394,11 +414,7 @@ __device__ void exporter_warp(unsigned char *smem, const Params &P, int lane) {
     mbar_arrive(bar_empty(bars, 1, e));
     if (t >= kRX) {  // the previous CTA has imported row t-kRX
       const unsigned need_x = (unsigned)(t - kRX + 1);
-      unsigned tries = 0;
-      while (xc_seen < need_x) {
-        xc_seen = ld_flag_s(xcredit);
-        if (++tries > kSpinCap) __trap();
-      }
+      for (SpinGuard guard; xc_seen < need_x; guard.poll()) xc_seen = ld_flag_s(xcredit);
     }
     unsigned long long *ex = xdst + (size_t)(t & (kRX - 1)) * 3 * DPAD;
     lv_st_ll<NV, VW>(B0, ex, lane, (unsigned)(t + 1));
