@@ -63,6 +63,7 @@ constexpr int kLookMax = 4;       // rows of that ring the importer keeps loads 
 constexpr int kFlagStride = 32;  // unsigned per counter: counters of different CTAs never share a line
 constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
 constexpr int kThreads = (kCols + 2) * 32;  // column slots + importer + exporter
+constexpr int kExporterBox = kCols + 1;      // barrier index of the exporter's inbox (never a consumer slot)
 // A polling loop that makes no progress for kSpinSeconds of wall clock traps instead of hanging
 // the GPU (a bug, not a slow neighbour: profilers and time-slicing can stall a CTA for a long
 // time, so the guard is on %globaltimer, looked at every 4096 polls, not on an iteration count).
@@ -155,7 +156,11 @@ __device__ __forceinline__ bool mbar_try(unsigned bar, unsigned parity) {
       "}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;
 }
-// barrier addresses: full(s, e) and empty(s, e) for slot s (0..kCols+1) and ring row e
+// barrier addresses for slot s (0..kCols+1) and ring row e.  `full` is the INBOX of consumer s:
+// it completes when both of its inputs for that row are there (the vertical vector of slot s+1
+// and the diagonal of slot s+2: 2 x 32 arrivals, from one or two producers), so a consumer waits
+// once per row; index kExporterBox is the exporter's inbox (slots 0 and 1).  `empty` belongs to
+// producer s: its readers are done with ring row e.
 template <int R = kR>
 __device__ __forceinline__ unsigned bar_full(unsigned base, int s, int e) { return base + (unsigned)((s * R + e) * 16); }
 template <int R = kR>
@@ -349,8 +354,11 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
             for (int j = 0; j < VW; ++j) t.v[k][j] = __uint_as_float((unsigned)buf[i][v][k * VW + j]);
           lv_sts<NV, VW>(t, dst[v] + rr * DPAD, lane);
         }
-        mbar_arrive(bar_full<R>(bars, ncols, rr));
-        mbar_arrive(bar_full<R>(bars, ncols + 1, rr));
+        // vertical of slot ncols and diagonal of slot ncols+1 go to slot ncols-1, the diagonal
+        // of slot ncols to slot ncols-2
+        mbar_arrive(bar_full<R>(bars, ncols - 1, rr));
+        mbar_arrive(bar_full<R>(bars, ncols - 1, rr));
+        mbar_arrive(bar_full<R>(bars, ncols - 2, rr));
         if (tracing && c == kTraceCta && lane == 0 && r >= kTraceRow0 && r < kTraceRow0 + kTraceRows) {
           g_trace[15][r - kTraceRow0][0] = c1; g_trace[15][r - kTraceRow0][1] = clock64();
         }
@@ -404,8 +412,7 @@ __device__ void exporter_warp(unsigned char *smem, const Params &P, int lane) {
   for (int t = 0; t < nrows; ++t) {
     const int e = t & (kR - 1);
     const unsigned par = (unsigned)((t / kR) & 1);
-    mbar_wait(bar_full(bars, 0, e), par);
-    mbar_wait(bar_full(bars, 1, e), par);
+    mbar_wait(bar_full(bars, kExporterBox, e), par);  // slots 0 and 1 have published row t
     LaneVec<NV, VW> B0, C0, C1;
     lv_lds<NV, VW>(B0, ringB + e * DPAD, lane);
     lv_lds<NV, VW>(C0, ringC + e * DPAD, lane);
@@ -538,8 +545,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       mark(t, 0);
       if (sync) {
         const long long c0 = stats ? clock64() : 0;
-        mbar_wait(bar_full(bars, j + 1, er), parr);
-        mbar_wait(bar_full(bars, j + 2, er), parr);
+        mbar_wait(bar_full(bars, j, er), parr);  // both inputs of row t are there
         if (stats) st_dep += clock64() - c0;
       }
       mark(t, 1);
@@ -570,7 +576,10 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       }
       lv_sts<NV, VW>(LB, ringB + ew * DPAD, 0);
       lv_sts<NV, VW>(LC, ringC + ew * DPAD, 0);
-      mbar_arrive(bar_full(bars, j, ew));
+      // into the inbox of each reader: slot j-1 (vertical), slot j-2 (diagonal), the exporter
+      if (j >= 1) mbar_arrive(bar_full(bars, j - 1, ew));
+      if (j >= 2) mbar_arrive(bar_full(bars, j - 2, ew));
+      if (j < 2) mbar_arrive(bar_full(bars, kExporterBox, ew));
       mark(t, 2);
     }
 
@@ -623,7 +632,7 @@ __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P)
     const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
     const int sl = threadIdx.x / kR, e = threadIdx.x % kR;
     const int readers = slot_readers(sl, ncols);
-    mbar_init(bar_full(bars, sl, e), 32u);                             // every lane of the writer
+    mbar_init(bar_full(bars, sl, e), 64u);                             // two inputs x every lane of their writer
     mbar_init(bar_empty(bars, sl, e), readers ? 32u * readers : 1u);   // every lane of each reader
   }
   if (threadIdx.x == 0) *reinterpret_cast<unsigned *>(smem + C::kCreditOff) = 0u;
