@@ -136,6 +136,62 @@ __device__ __forceinline__ void lv_sgm_step(LaneVec<NV, VW> &L, const LaneVec<NV
     }
 }
 
+// Packed fp32 pair arithmetic (FADD2 on sm_100a: add.rn.f32x2, same rounding as two FADDs).
+__device__ __forceinline__ void f2_add(float &d0, float &d1, float a0, float a1, float b0, float b1) {
+  unsigned long long ra, rb, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b0), "f"(b1));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(rd));
+}
+__device__ __forceinline__ void f2_sub(float &d0, float &d1, float a0, float a1, float b0, float b1) {
+  unsigned long long ra, rb, rd;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(ra) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(rb) : "f"(b0), "f"(b1));
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(rd));
+}
+
+// lv_sgm_step with the additions issued as packed pairs (VW even): identical results, 7 FADD2
+// instead of 14 FADD per 4 values.  For kernels that are bound by issue slots (sgm_vsweep.cu).
+template <int NV, int VW>
+__device__ __forceinline__ void lv_sgm_step_packed(LaneVec<NV, VW> &L, const LaneVec<NV, VW> &c, float p1,
+                                                   float p2_adj, const LaneCtx &cx) {
+  static_assert(VW % 2 == 0, "packed step needs an even vector width");
+  const float m = lv_min<NV, VW>(L, cx);
+  float from_left[NV], from_right[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    from_left[k] = __shfl_sync(FULL, L.v[k][VW - 1], cx.src_lo);
+    from_right[k] = __shfl_sync(FULL, L.v[k][0], cx.src_hi);
+  }
+  const float far = __fadd_rn(m, p2_adj);
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    // values at d-1 of the first element and d+1 of the last one (+inf outside [0, Dpad))
+    const float lo0 = cx.first ? (k > 0 ? from_left[k > 0 ? k - 1 : 0] : CUDART_INF_F) : from_left[k];
+    const float hiN = cx.last ? (k < NV - 1 ? from_right[k < NV - 1 ? k + 1 : k] : CUDART_INF_F) : from_right[k];
+    float Lp[VW];  // L[j] + p1: the left neighbour term of j+1 and the right neighbour term of j-1
+#pragma unroll
+    for (int j = 0; j < VW; j += 2) f2_add(Lp[j], Lp[j + 1], L.v[k][j], L.v[k][j + 1], p1, p1);
+    float e0, e1;  // the two terms that come from the neighbouring lanes
+    f2_add(e0, e1, lo0, hiN, p1, p1);
+    float best[VW];
+#pragma unroll
+    for (int j = 0; j < VW; ++j) {
+      const float a = j > 0 ? Lp[j - 1] : e0;
+      const float b = j < VW - 1 ? Lp[j + 1] : e1;
+      best[j] = fminf(fminf(L.v[k][j], a), fminf(b, far));
+    }
+#pragma unroll
+    for (int j = 0; j < VW; j += 2) {
+      float s0, s1;
+      f2_add(s0, s1, c.v[k][j], c.v[k][j + 1], best[j], best[j + 1]);
+      f2_sub(L.v[k][j], L.v[k][j + 1], s0, s1, m, m);
+    }
+  }
+}
+
 // max(P1, P2/|dI|) with std::max semantics (x/0 = inf, 0/0 = NaN -> P1), IEEE division.
 __device__ __forceinline__ float sgm_p2_adjusted(float p1, float p2, float intensity, float prev) {
   const float q = __fdiv_rn(p2, fabsf(__fsub_rn(intensity, prev)));

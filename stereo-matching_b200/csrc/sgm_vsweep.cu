@@ -188,6 +188,15 @@ __device__ __forceinline__ unsigned ld_relaxed_g(const unsigned *p) {
 __device__ __forceinline__ void st_relaxed_g(unsigned *p, unsigned v) {
   asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
+// The recurrence with packed additions where the lane map allows it (this kernel is bound by
+// issue slots; the per-direction kernels are not and keep lv_sgm_step).
+template <int NV, int VW>
+__device__ __forceinline__ void sgm_step(LaneVec<NV, VW> &L, const LaneVec<NV, VW> &c, float p1, float p2_adj,
+                                         const LaneCtx &cx) {
+  if constexpr (VW % 2 == 0) lv_sgm_step_packed<NV, VW>(L, c, p1, p2_adj, cx);
+  else lv_sgm_step<NV, VW>(L, c, p1, p2_adj, cx);
+}
+
 // ---- (value, tag) words ---------------------------------------------------------------------
 __device__ __forceinline__ unsigned long long ll_pack(float v, unsigned tag) {
   return ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
@@ -435,9 +444,15 @@ template <int NV, int VW>
 __device__ __forceinline__ void add_weighted(LaneVec<NV, VW> &o, const LaneVec<NV, VW> &L, int mult) {
   if (mult == 1) {
 #pragma unroll
-    for (int k = 0; k < NV; ++k)
+    for (int k = 0; k < NV; ++k) {
+      if constexpr (VW % 2 == 0) {
 #pragma unroll
-      for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+        for (int j = 0; j < VW; j += 2) f2_add(o.v[k][j], o.v[k][j + 1], o.v[k][j], o.v[k][j + 1], L.v[k][j], L.v[k][j + 1]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+      }
+    }
   } else if (mult != 0) {
     const float w = (float)mult;
 #pragma unroll
@@ -554,9 +569,9 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       mbar_arrive(bar_empty(bars, j + 1, er));
       mbar_arrive(bar_empty(bars, j + 2, er));
       // straight-line so the three recurrences interleave; a path start is a select
-      lv_sgm_step<NV, VW>(LB, c, p1, pb, cx);
-      lv_sgm_step<NV, VW>(LC, c, p1, pc, cx);
-      lv_sgm_step<NV, VW>(LA, c, p1, pa, cx);
+      sgm_step<NV, VW>(LB, c, p1, pb, cx);
+      sgm_step<NV, VW>(LC, c, p1, pc, cx);
+      sgm_step<NV, VW>(LA, c, p1, pa, cx);
       const bool startC = x == W - 1, startA = x == 0;
 #pragma unroll
       for (int k = 0; k < NV; ++k)
