@@ -496,7 +496,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int off = k * 32 * VW;
-      if (VW > 1 || off + lane < D) {
+      if ((VW > 1 || off + lane < D) && !(kDebug && (P.dbg & 32))) {
         cp_async<VW * 4>(dc + off, cs + off);
         cp_async<VW * 4>(dc + DPAD + off, ss + off);
       }
@@ -616,7 +616,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       add_weighted<NV, VW>(o, LC, sgm_mult5(x, y, H, W));
       add_weighted<NV, VW>(o, LA, sgm_mult7(x, y, H, W));
     }
-    if (store_vol) lv_store<NV, VW, true>(o, orow + x * D, 0, D - lane_off);
+    if (store_vol && !(kDebug && (P.dbg & 32))) lv_store<NV, VW, true>(o, orow + x * D, 0, D - lane_off);
     if (emit_wta) lv_argmin_store<NV, VW>(o, lane, D, drow + x);
 
     mark(t, 3);
