@@ -551,6 +551,16 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
     const int e_refill = e;
     e = en;
 
+    // ring row t of this slot must be free (its readers consumed row t-kR): checked here, off
+    // the hand-off path -- it has normally been true for a while
+    {
+      const int ew = t & (kR - 1);
+      if (t >= kR && sync) {  // ring row t-kR has been read by slots j-1, j-2
+        const long long c0 = stats ? clock64() : 0;
+        mbar_wait(bar_empty(bars, j, ew), (unsigned)(((t >> 2) - 1) & 1));
+        if (stats) st_cred += clock64() - c0;
+      }
+    }
     LaneVec<NV, VW> LB, LC;
     if constexpr (FIRST) {
       LB = c; LC = c; LA = c;
@@ -568,27 +578,18 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       lv_lds<NV, VW>(LC, ringC + 2 * kR * DPAD + er * DPAD, 0);
       mbar_arrive(bar_empty(bars, j + 1, er));
       mbar_arrive(bar_empty(bars, j + 2, er));
-      // straight-line so the three recurrences interleave; a path start is a select
+      // the two recurrences the neighbours wait for, interleaved; a path start is a select
       sgm_step<NV, VW>(LB, c, p1, pb, cx);
       sgm_step<NV, VW>(LC, c, p1, pc, cx);
-      sgm_step<NV, VW>(LA, c, p1, pa, cx);
-      const bool startC = x == W - 1, startA = x == 0;
+      const bool startC = x == W - 1;
 #pragma unroll
       for (int k = 0; k < NV; ++k)
 #pragma unroll
-        for (int q = 0; q < VW; ++q) {
-          LC.v[k][q] = startC ? c.v[k][q] : LC.v[k][q];
-          LA.v[k][q] = startA ? c.v[k][q] : LA.v[k][q];
-        }
+        for (int q = 0; q < VW; ++q) LC.v[k][q] = startC ? c.v[k][q] : LC.v[k][q];
     }
 
     {  // hand the vertical and the u+2 diagonal to slots j-1, j-2 (the last row's go nowhere)
       const int ew = t & (kR - 1);
-      if (t >= kR && sync) {  // ring row t-kR has been read by slots j-1, j-2
-        const long long c0 = stats ? clock64() : 0;
-        mbar_wait(bar_empty(bars, j, ew), (unsigned)(((t >> 2) - 1) & 1));
-        if (stats) st_cred += clock64() - c0;
-      }
       lv_sts<NV, VW>(LB, ringB + ew * DPAD, 0);
       lv_sts<NV, VW>(LC, ringC + ew * DPAD, 0);
       // into the inbox of each reader: slot j-1 (vertical), slot j-2 (diagonal), the exporter
@@ -598,8 +599,16 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       mark(t, 2);
     }
 
-    // Off the hand-off path: refill the prefetch entry just consumed with row t + PF, then this
-    // row's sum / store / argmin.
+    // Off the hand-off path: the register-held diagonal (nobody's input), the refill of the
+    // prefetch entry just consumed with row t + PF, then this row's sum / store / argmin.
+    if constexpr (!FIRST) {
+      sgm_step<NV, VW>(LA, c, p1, pa, cx);
+      const bool startA = x == 0;
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int q = 0; q < VW; ++q) LA.v[k][q] = startA ? c.v[k][q] : LA.v[k][q];
+    }
     asm volatile("" ::: "memory");
     issue(e_refill);
     pa = pn.x; pb = pn.y; pc = pn.z;
