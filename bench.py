@@ -130,6 +130,28 @@ def cpu_reference_sample(rows: int, seed: int = 1000):
     return dt, rows * W * D, kind, 1
 
 
+# stdout carries exactly ONE JSON line.  Native libraries print there too (NCCL's "NCCL version ..."
+# banner when NCCL_DEBUG is set on the box), so file descriptor 1 is pointed at stderr for the
+# whole run and the line is written to the saved descriptor.
+_JSON_FD = None
+
+
+def _claim_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -157,7 +179,7 @@ def run_reference_arm(args):
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -342,7 +364,7 @@ def run_b200_arm(args):
         "stages": stages,
         "cpu_baseline": cpu_baseline,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -379,6 +401,7 @@ def main():
     ap.add_argument("--ref-rows", type=int, default=64, help="rows per step of --impl reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    _claim_stdout()
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_b200_arm(args)
