@@ -59,6 +59,10 @@ constexpr int kRX = 16;        // rows in the CTA->CTA ring
 #define STM_VSWEEP_PF 5
 #endif
 constexpr int kPfSmall = STM_VSWEEP_PF;
+#ifndef STM_VSWEEP_LOOK
+#define STM_VSWEEP_LOOK 1
+#endif
+constexpr int kImporterLook = STM_VSWEEP_LOOK;  // 1: measured, see importer_core
 constexpr int kLookMax = 4;       // rows of that ring the importer keeps loads in flight for
 constexpr int kFlagStride = 32;  // unsigned per counter: counters of different CTAs never share a line
 constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
@@ -313,11 +317,6 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
   const bool poll = !kDebug || !(P.dbg & 1), stats = kDebug && (P.dbg & 8) != 0;
   const bool tracing = kDebug && (P.dbg & 16) != 0;
   unsigned long long st_polls = 0, st_ready = 0, st_credit = 0, st_rtt = 0;
-  // The slots that export (0, 1) have prefetches in flight and were measured to wait ~6 us for
-  // a global flag read; the importer has none, so it fetches their credit (rows the PREVIOUS
-  // CTA has imported) every row, one row ahead of publishing it in shared memory.
-  const unsigned *xcred_src = &P.xcons[(size_t)(c == 0 ? P.G - 1 : c - 1) * kFlagStride];
-  unsigned cred = ld_relaxed_g(xcred_src);
   // kLook rows of (value, tag) words in flight: the L2 round trip is longer than a row
 #pragma unroll
   for (int i = 0; i < kLook; ++i) load(buf[i], i < nrows ? i : nrows - 1);
@@ -328,18 +327,11 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
       const int r = r0 + i;
       if (r < nrows) {
         const int rr = r & (R - 1);
-        if (lane == 0) st_flag_s(xcred_dst, cred);
-        cred = ld_relaxed_g(xcred_src);
         long long c0 = (stats || tracing) ? clock64() : 0;
         if (r >= R && poll) {  // the readers of ring row r-R are done with it
           const unsigned par = (unsigned)(((r / R) - 1) & 1);
-          // keep the exporters' credit fresh while waiting: they may be what the readers of
-          // these ring rows are (transitively) waiting for -- a stale credit would deadlock
-          while (!mbar_try(bar_empty<R>(bars, ncols, rr), par) ||
-                 !mbar_try(bar_empty<R>(bars, ncols + 1, rr), par)) {
-            if (lane == 0) st_flag_s(xcred_dst, cred);
-            cred = ld_relaxed_g(xcred_src);
-          }
+          mbar_wait(bar_empty<R>(bars, ncols, rr), par);
+          mbar_wait(bar_empty<R>(bars, ncols + 1, rr), par);
         }
         long long c1 = (stats || tracing) ? clock64() : 0;
         unsigned tries = 0;
@@ -348,8 +340,6 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
           ++tries;
           guard.poll();
           const long long r0 = stats ? clock64() : 0;
-          if (lane == 0) st_flag_s(xcred_dst, cred);
-          cred = ld_relaxed_g(xcred_src);
           load(buf[i], r);
           if (stats) { (void)ready(buf[i], r); st_rtt += clock64() - r0; }
         }
@@ -378,12 +368,6 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
       }
     }
   }
-  // the exporters' last credit: the previous CTA has imported row H-2-kRX
-  for (SpinGuard guard;; guard.poll()) {
-    if (lane == 0) st_flag_s(xcred_dst, cred);
-    if ((int)cred >= nrows - kRX) break;
-    cred = ld_relaxed_g(xcred_src);
-  }
   if (stats && lane == 0) {
     stat_add(0, (unsigned long long)nrows); stat_add(1, st_polls); stat_add(2, st_ready);
     stat_add(3, st_credit); stat_add(4, st_rtt);
@@ -395,7 +379,7 @@ __device__ void importer_warp(unsigned char *smem, const Params &P, int ncols, i
   constexpr int DPAD = NV * 32 * VW, NE = NV * VW;
   using C = Cfg<DPAD>;
   // rows of (value, tag) words in flight, bounded by registers (3 vectors x NE words per lane each)
-  constexpr int LOOK = NE <= 4 ? kLookMax : (NE <= 6 ? 2 : 1);
+  constexpr int LOOK = kImporterLook;
   importer_core<NV, VW, kR, LOOK>((unsigned)__cvta_generic_to_shared(smem + C::kBarOff),
                                   reinterpret_cast<float *>(smem + C::kRingBOff),
                                   reinterpret_cast<float *>(smem + C::kRingCOff),
@@ -412,7 +396,9 @@ __device__ void exporter_warp(unsigned char *smem, const Params &P, int lane) {
   using C = Cfg<DPAD>;
   const int nrows = P.H - 1;  // the last row's vectors have no consumer
   const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
-  const unsigned *xcredit = reinterpret_cast<const unsigned *>(smem + C::kCreditOff);
+  // rows the previous CTA's importer has taken out of this CTA's ring (the exporter has no
+  // other global traffic, so the read costs one L2 round trip, every ~14 rows)
+  const unsigned *xcredit = &P.xcons[(size_t)(blockIdx.x == 0 ? P.G - 1 : blockIdx.x - 1) * kFlagStride];
   const float *ringB = reinterpret_cast<const float *>(smem + C::kRingBOff);
   const float *ringC = reinterpret_cast<const float *>(smem + C::kRingCOff);
   unsigned long long *xdst = P.xring + (size_t)blockIdx.x * kRX * 3 * DPAD;
@@ -430,7 +416,7 @@ __device__ void exporter_warp(unsigned char *smem, const Params &P, int lane) {
     mbar_arrive(bar_empty(bars, 1, e));
     if (t >= kRX) {  // the previous CTA has imported row t-kRX
       const unsigned need_x = (unsigned)(t - kRX + 1);
-      for (SpinGuard guard; xc_seen < need_x; guard.poll()) xc_seen = ld_flag_s(xcredit);
+      for (SpinGuard guard; xc_seen < need_x; guard.poll()) xc_seen = ld_relaxed_g(xcredit);
     }
     unsigned long long *ex = xdst + (size_t)(t & (kRX - 1)) * 3 * DPAD;
     lv_st_ll<NV, VW>(B0, ex, lane, (unsigned)(t + 1));
