@@ -29,7 +29,7 @@ class Semiglobal:
         component as two fused sweeps (csrc/sgm_vsweep.cu): four passes over the volumes instead
         of eight.  The sum is associated per sweep (0, 1, 2+4+6, 3+5+7) -- within 1e-4 of the
         reference order (measured 1.3e-5 at 1080p), not bit-identical.  fused_sweeps=None
-        (default) uses them for volumes above 48 MB whose rows hold at least 896*128 values
+        (default) uses them for volumes above 48 MB whose rows hold at least 704*128 values
         (where they are faster), True always, False never (reference order).
         Shapes the sweeps do not handle (more than 13 columns per SM, D not in {<=32, 64, 128,
         192, 256}) take the per-direction passes.
@@ -46,12 +46,12 @@ class Semiglobal:
 
     def _use_fused_sweeps(self, cost_volume: torch.Tensor) -> bool:
         if self.fused_sweeps is None:
-            # auto.  A sweep costs ~0.95 us per image row whatever the row holds (hand-off
-            # latency), a direction pass costs its bytes: measured break-even at 1080 rows is
-            # W*D ~ 110k (960x128: equal, 1300x128 and 1920x64: sweeps 10 % faster, 480x128: 2x
-            # slower); below 48 MB the concurrent directions win anyway.
+            # auto.  A sweep costs ~0.7 us per image row almost whatever the row holds (hand-off
+            # latency), a direction pass costs its bytes: break-even at 1080 rows is W*D ~ 90k
+            # (measured ~110k when the sweeps took 0.93 us per row; scaled); below 48 MB the
+            # concurrent directions win anyway.
             H, W, D = cost_volume.shape
-            return cost_volume.numel() * cost_volume.element_size() > (48 << 20) and W * D >= 896 * 128
+            return cost_volume.numel() * cost_volume.element_size() > (48 << 20) and W * D >= 704 * 128
         return bool(self.fused_sweeps)
 
     def __call__(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
