@@ -13,7 +13,11 @@ One JSON line is printed by rank 0:
   e2e       same metric with HOST buffers through stereomatch.streaming.HostFrameStreamer:
             pinned H2D of both images and D2H of the disparity map inside the timed
             region, every frame (copies overlap the previous/next frame's compute)
-  roofline  dominant stage (SGM) against the measured HBM copy bandwidth
+  roofline  dominant stage (SGM) against the measured HBM copy bandwidth: algorithmic bytes over
+            the MEDIAN stand-alone stage time (each stage warmed up first), every pass listed
+  stages    SSD / SGM / WTA stand-alone, median CUDA-event time, fraction of the roofline
+  configs   BASELINE.json configs 2, 3, 4 (one frame each, per stage and whole frame)
+  config5   the 64-frame 1080p D=192 batch sharded over the ranks of this run (strong scaling)
   cpu_baseline  the unmodified reference CPU ops (oracle/_ref) on a bounded sample
 `--impl reference` times the reference's own CPU implementation (rank 0 only).
 """
@@ -37,6 +41,7 @@ KERNEL_SIZE, P1, P2 = 7, 0.1, 0.2
 METRIC = "Gpix-disp/s (H*W*D) SSD+SGM+WTA 1080p D=128"
 # algorithmic (compulsory) bytes per pixel-disparity, SURVEY.md 8(d) / DESIGN.md
 ALGO_BYTES = {"ssd": 4.0 + 8.0 / D, "sgm": 8.0 + 4.0 / D, "wta": 4.0 + 4.0 / D}
+STAGE_WARM = 3   # untimed launches of every stand-alone stage before its timed ones
 
 
 def measured_peak():
@@ -267,52 +272,163 @@ def run_b200_arm(args):
         step_e2e()
     ms_e2e, _, _ = timed(step_e2e, args.steps)
 
-    # per-stage device times (CUDA events on the launching stream), for the roofline
-    stage_ms = {"ssd": 0.0, "sgm": 0.0, "wta": 0.0}
-    reps = max(3, min(args.steps, 10))
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-    l, r = dev_frames[0]
-    for rep in range(reps):
-        l, r = dev_frames[rep % F]
-        ev[0].record()
-        cost = ssd(l, r, cost_volume=pipe._cost_volume)
-        ev[1].record()
-        agg = sgm(cost, l, pipe._aggregation_volume)
-        ev[2].record()
-        wta(agg, pipe._disparity_image)
-        ev[3].record()
-        torch.cuda.synchronize()
-        stage_ms["ssd"] += ev[0].elapsed_time(ev[1]) / reps
-        stage_ms["sgm"] += ev[1].elapsed_time(ev[2]) / reps
-        stage_ms["wta"] += ev[2].elapsed_time(ev[3]) / reps
-    sgm_launches0 = C.launch_count()
-    sgm(cost, l, pipe._aggregation_volume)
-    sgm_launches = C.launch_count() - sgm_launches0
-    torch.cuda.synchronize()
+    # ---- per-stage device times (CUDA events on the launching stream), for the roofline ----
+    # Every stand-alone stage is launched `STAGE_WARM` times untimed first (the variants timed
+    # here -- unfused SGM, the WTA kernel -- are not the ones Pipeline.estimate ran above: their
+    # first launch pays module loading and a new per-stream workspace), then timed `reps` times,
+    # one event pair per launch, and the MEDIAN is reported.
+    reps = max(5, min(args.steps, 20))
 
-    # every direction pass of the dominant stage on its own: CUDA events recorded by the
-    # library on the launching stream around each pass (stm_sgm_pass_timing)
-    pass_ms = {}
-    C.AggregationOps.pass_timing(True)
-    for rep in range(reps):
-        l, r = dev_frames[rep % F]
-        sgm(cost, l, pipe._aggregation_volume)
-        for k, (d, t) in enumerate(C.AggregationOps.last_pass_ms()):
-            pass_ms.setdefault((k, d), []).append(t)
-    C.AggregationOps.pass_timing(False)
+    def stage_ms(fn):
+        for _ in range(STAGE_WARM):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            ts.append(a.elapsed_time(b))
+        ts.sort()
+        return ts[len(ts) // 2]
+
+    def pass_times(sgm_op, cost, img, out):
+        """Median CUDA-event time of every pass of one stand-alone aggregation (the library
+        records the events on the launching stream: stm_sgm_pass_timing)."""
+        acc = {}
+        C.AggregationOps.pass_timing(True)
+        try:
+            for _ in range(STAGE_WARM + reps):
+                sgm_op(cost, img, out)
+                for k, (d, t) in enumerate(C.AggregationOps.last_pass_ms()):
+                    acc.setdefault((k, d), []).append(t)
+        finally:
+            C.AggregationOps.pass_timing(False)
+        return {kd: sorted(ts[STAGE_WARM:])[len(ts[STAGE_WARM:]) // 2] for kd, ts in acc.items()}
+
+    peak, peak_kind = measured_peak()
+
+    def stage_record(ms_, algo_bytes_per_pd, n_pd):
+        gbs = algo_bytes_per_pd * n_pd / (ms_ * 1e-3) / 1e9
+        return {"ms": round(ms_, 4), "algo_GBs": round(gbs, 1), "frac": round(gbs / peak, 4),
+                "Gpix_disp_s": round(n_pd / (ms_ * 1e-3) / 1e9, 2)}
+
+    N = H * W * D
+    l, r = dev_frames[0]
+    cost = ssd(l, r, cost_volume=pipe._cost_volume)
+    vol = pipe._aggregation_volume
+    ms_ssd = stage_ms(lambda: ssd(l, r, cost_volume=cost))
+    ms_sgm = stage_ms(lambda: sgm(cost, l, vol))
+    agg = sgm(cost, l, vol)
+    ms_wta = stage_ms(lambda: wta(agg, dev_out[0]))
+    # what Pipeline.estimate runs for SGM + WTA: one call, argmin in the last pass, no write-back
+    ms_fused = stage_ms(lambda: sgm.aggregate_and_reduce(cost, l, vol, dev_out[0], keep_volume=False))
+    sgm_launches0 = C.launch_count()
+    sgm(cost, l, vol)
+    sgm_launches = C.launch_count() - sgm_launches0
+    pass_ms = pass_times(sgm, cost, l, vol)
+    torch.cuda.synchronize()
+    stage_t = {"ssd": ms_ssd, "sgm": ms_sgm, "wta": ms_wta}
+    stages = {k: stage_record(v, ALGO_BYTES[k], N) for k, v in stage_t.items()}
+    stages["sgm_wta_fused_call"] = {"ms": round(ms_fused, 4),
+                                    "note": "stm_sgm_wta_f32 + STM_SGM_DISPARITY_ONLY, what Pipeline.estimate runs"}
+
+    passes = []
+    fused = len(pass_ms) == 4  # horizontal passes + two fused vertical sweeps (sgm_vsweep.cu)
+    for (k, d), t in sorted(pass_ms.items()):
+        b = sgm_pass_bytes(d, k == 0, H, W, D, fused_sweep=fused and k >= 2)
+        label = {2: "2+4+6", 3: "3+5+7"}[d] if fused and k >= 2 else str(d)
+        passes.append({"dir": label, "ms": round(t, 4), "bytes": b, "GBs": round(b / (t * 1e-3) / 1e9, 1),
+                       "frac_of_peak": round(b / (t * 1e-3) / 1e9 / peak, 3)})
+    sum_passes = sum(p_["ms"] for p_ in passes)
+    # the stage time and the sum of its passes are two measurements of the same thing
+    passes_agree = abs(sum_passes - ms_sgm) <= 0.10 * ms_sgm + 0.05
+
+    # ---- the other BASELINE.json configs, one frame each (parity: tests/test_gpu_named_shapes.py) ----
+    def run_config(Hc, Wc, Dc, cost_kind, reducer, label, l2_note=None):
+        from oracle import synth
+        lh, rh, _ = synth.random_dot_pair(Hc, Wc, Dc, seed=1000, scale="raw")
+        lc, rc = torch.from_numpy(lh).to(dev), torch.from_numpy(rh).to(dev)
+        n_pd = Hc * Wc * Dc
+        cost_op = stereomatch.cost.SSD(Dc, KERNEL_SIZE) if cost_kind == "ssd" else stereomatch.cost.Birchfield(Dc)
+        rec = {"shape": f"{Wc}x{Hc} D={Dc}", "stages": {}}
+        cvol = cost_op(lc, rc)
+        rec["stages"][cost_kind] = stage_record(stage_ms(lambda: cost_op(lc, rc, cost_volume=cvol)),
+                                                4.0 + 8.0 / Dc, n_pd)
+        if reducer == "wta":
+            sg = stereomatch.aggregation.Semiglobal(P1, P2)
+            wt = stereomatch.disparity_reduce.WinnerTakesAll()
+            avol = sg(cvol, lc)
+            rec["stages"]["sgm"] = stage_record(stage_ms(lambda: sg(cvol, lc, avol)), 8.0 + 4.0 / Dc, n_pd)
+            dimg = wt(avol)
+            rec["stages"]["wta"] = stage_record(stage_ms(lambda: wt(avol, dimg)), 4.0 + 4.0 / Dc, n_pd)
+            p_ = stereomatch.Pipeline(cost_op, wt, sg)
+            p_._cost_volume, p_._aggregation_volume, p_._disparity_image = cvol, avol, dimg
+            algo = (4.0 + 8.0 / Dc) + (8.0 + 4.0 / Dc) + (4.0 + 4.0 / Dc)
+        else:
+            algo_dp = 5.0 + (8.0 * Hc * Dc + 5.0 * Hc * Wc) / n_pd
+            for mode in ("cuda", "cpu_exact"):
+                dpo = stereomatch.disparity_reduce.DynamicProgramming(mode=mode)
+                dimg = dpo(cvol)
+                rec["stages"]["dp" if mode == "cuda" else "dp_cpu_exact"] = stage_record(
+                    stage_ms(lambda: dpo(cvol, dimg)), algo_dp, n_pd)
+            p_ = stereomatch.Pipeline(cost_op, stereomatch.disparity_reduce.DynamicProgramming())
+            p_._cost_volume = cvol
+            algo = (4.0 + 8.0 / Dc) + algo_dp
+        frame = stage_ms(lambda: p_.estimate(lc, rc))
+        rec["frame"] = stage_record(frame, algo, n_pd)
+        rec["frame"]["note"] = "Pipeline.estimate, one frame in flight, device-resident"
+        if l2_note:
+            rec["l2"] = l2_note
+        rec["workload"] = label
+        torch.cuda.synchronize()
+        return rec
+
+    configs = {}
+    if not args.no_configs:
+        configs["config2"] = run_config(375, 450, 64, "ssd", "wta", "450x375 D=64 SSD+SGM+WTA",
+                                        l2_note="L2-resident (43 MB volumes): not HBM-roofline evidence")
+        configs["config3"] = run_config(H, W, D, "birchfield", "wta", "1920x1080 D=128 Birchfield+SGM+WTA")
+        configs["config4"] = run_config(H, W, D, "ssd", "dp", "1920x1080 D=128 SSD+DP (default and cpu_exact)")
+
+    # ---- config 5: the 64-frame D=192 video batch, frame-sharded over the ranks of THIS run ----
+    config5 = None
+    if not args.no_configs:
+        from oracle import synth
+        D5, F5 = 192, args.config5_frames
+        b5, e5 = sharding.shard_range(F5, rank, world)
+        mine = [synth.random_dot_pair(H, W, D5, seed=1000 + f, scale="raw")[:2] for f in range(b5, e5)]
+        dev5 = [(torch.from_numpy(a).to(dev), torch.from_numpy(b).to(dev)) for a, b in mine]
+        out5 = [torch.empty(H, W, dtype=torch.int32, device=dev) for _ in dev5]
+        mk5 = lambda: stereomatch.Pipeline(stereomatch.cost.SSD(D5, KERNEL_SIZE),
+                                           stereomatch.disparity_reduce.WinnerTakesAll(),
+                                           stereomatch.aggregation.Semiglobal(P1, P2))
+        batch5 = stereomatch.streaming.BatchEstimator([mk5(), mk5()], dev)
+        for _ in range(2):
+            batch5.estimate_batch(dev5[:4], out5[:4])
+        ms5, _, _ = timed(lambda: batch5.estimate_batch(dev5, out5), 1)
+        ms5b, _, _ = timed(lambda: batch5.estimate_batch(dev5, out5), 1)
+        ms5 = min(ms5, ms5b)
+        n5 = H * W * D5
+        config5 = {"workload": f"{F5} x (1920x1080 D={D5}) SSD+SGM+WTA, frames [{b5},{e5}) on rank 0 of {world}",
+                   "frames": F5, "n_gpus": world, "ms_per_batch": round(ms5, 3),
+                   "ms_per_frame_per_gpu": round(ms5 / max(e5 - b5, 1), 4),
+                   "Gpix_disp_s": round(F5 * n5 / (ms5 * 1e-3) / 1e9, 2),
+                   "scaling": "strong (fixed 64-frame batch split over the ranks), no collective",
+                   "timing": "CUDA events, barrier both sides, max over ranks, best of 2 batches"}
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return 0
 
-    N = H * W * D
     total_px = N * F * world * args.steps
     value = total_px / (ms * 1e-3) / 1e9
     e2e = total_px / (ms_e2e * 1e-3) / 1e9
-    peak, peak_kind = measured_peak()
-    dom = max(stage_ms, key=stage_ms.get)
-    achieved = ALGO_BYTES[dom] * N / (stage_ms[dom] * 1e-3) / 1e9
+    dom = max(stage_t, key=stage_t.get)
+    achieved = ALGO_BYTES[dom] * N / (stage_t[dom] * 1e-3) / 1e9
     traffic = None
     tp = ROOT / "profiles" / "traffic.json"
     if tp.exists():
@@ -320,17 +436,6 @@ def run_b200_arm(args):
             traffic = json.loads(tp.read_text()).get(dom)
         except Exception:
             traffic = None
-    passes = []
-    fused = len(pass_ms) == 4  # horizontal passes + two fused vertical sweeps (sgm_vsweep.cu)
-    for (k, d), ts in sorted(pass_ms.items()):
-        t = sorted(ts)[len(ts) // 2]
-        b = sgm_pass_bytes(d, k == 0, H, W, D, fused_sweep=fused and k >= 2)
-        label = {2: "2+4+6", 3: "3+5+7"}[d] if fused and k >= 2 else str(d)
-        passes.append({"dir": label, "ms": round(t, 4), "bytes": b, "GBs": round(b / (t * 1e-3) / 1e9, 1),
-                       "frac_of_peak": round(b / (t * 1e-3) / 1e9 / peak, 3)})
-    stages = {k: {"ms": round(v, 4), "algo_GBs": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9, 1),
-                  "frac": round(ALGO_BYTES[k] * N / (v * 1e-3) / 1e9 / peak, 4)}
-              for k, v in stage_ms.items()}
 
     cpu_baseline = None
     if not args.no_cpu_baseline:
@@ -358,15 +463,23 @@ def run_b200_arm(args):
         "roofline": {"bound": "hbm", "kernel": f"{dom} stage ({sgm_launches} launches)" if dom == "sgm" else dom,
                      "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
+                     "stage_ms": round(stage_t[dom], 4), "algo_bytes": ALGO_BYTES[dom] * N,
+                     "timing": f"median of {reps} launches after {STAGE_WARM} untimed, CUDA events",
                      # what each pass of the stage HAS to move (C read, S read-modify-write;
                      # the first pass only writes) over its own duration
-                     "passes": passes},
+                     "passes": passes, "sum_passes_ms": round(sum_passes, 4),
+                     "passes_agree_with_stage": bool(passes_agree)},
         "stages": stages,
+        "configs": configs,
+        "config5": config5,
         "cpu_baseline": cpu_baseline,
     }
     _emit(line)
     if world > 1:
         dist.destroy_process_group()
+    if not passes_agree:
+        print(f"bench.py: sum of SGM passes {sum_passes:.3f} ms vs stage {ms_sgm:.3f} ms disagree",
+              file=sys.stderr)
     return 0
 
 
@@ -400,6 +513,8 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=160, help="rows of the cpu_baseline crop")
     ap.add_argument("--ref-rows", type=int, default=64, help="rows per step of --impl reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the configs 2-5 block")
+    ap.add_argument("--config5-frames", type=int, default=64, help="frames of the D=192 batch (config 5)")
     args = ap.parse_args()
     _claim_stdout()
     if args.impl == "reference":

@@ -57,6 +57,90 @@ def ssd(left, right, max_disparity: int, kernel_size: int = 7) -> np.ndarray:
     return cost
 
 
+def _row_chunks(H: int, threads: int):
+    n = max(1, min(int(threads), H))
+    edges = [round(i * H / n) for i in range(n + 1)]
+    return [(a, b) for a, b in zip(edges[:-1], edges[1:]) if b > a]
+
+
+def default_threads() -> int:
+    import os
+    return max(1, min(32, os.cpu_count() or 1))
+
+
+def ssd_threaded(left, right, max_disparity: int, kernel_size: int = 7,
+                 threads: int | None = None) -> np.ndarray:
+    """stm_oracle_ssd over row chunks on a thread pool (ctypes releases the GIL).  Output row y
+    only reads image rows [y-k, y+k), so each chunk is the literal function on a slice of the
+    images: bit-identical to ssd() (tests/test_oracle_golden.py), just faster at 1080p."""
+    from concurrent.futures import ThreadPoolExecutor
+    left, right = _f32(left), _f32(right)
+    H, W = left.shape
+    k = int(kernel_size)
+    cost = np.empty((H, W, max_disparity), np.float32)
+
+    def work(ab):
+        a, b = ab
+        lo, hi = max(a - k, 0), min(b + k, H)
+        cost[a:b] = ssd(left[lo:hi], right[lo:hi], max_disparity, k)[a - lo:b - lo]
+
+    with ThreadPoolExecutor(threads or default_threads()) as ex:
+        list(ex.map(work, _row_chunks(H, (threads or default_threads()) * 4)))
+    return cost
+
+
+def ssd_exact_int(left, right, max_disparity: int, kernel_size: int = 7,
+                  threads: int | None = None) -> np.ndarray:
+    """SSD of INTEGER-VALUED images (the raw 0..255 scale) by int64 integral images.  Every
+    partial sum of the reference's fp32 loop (src/ssd.cu:44-56) is then an exact integer below
+    2^24 (196 * 255^2 = 12,744,900), so the reference's result is the exact integer sum whatever
+    the order: this returns exactly what ssd() returns (checked in tests/test_oracle_golden.py),
+    in seconds instead of a minute at 1080p.  Raises for non-integer images or sums >= 2^24."""
+    from concurrent.futures import ThreadPoolExecutor
+    left, right = _f32(left), _f32(right)
+    L, R = left.astype(np.int64), right.astype(np.int64)
+    if not (np.array_equal(L, left) and np.array_equal(R, right)):
+        raise ValueError("ssd_exact_int needs integer-valued images")
+    H, W = L.shape
+    k, D = int(kernel_size), int(max_disparity)
+    dmax = int(max(L.max(initial=0) - R.min(initial=0), R.max(initial=0) - L.min(initial=0)))
+    if (2 * k) * (2 * k) * dmax * dmax >= (1 << 24):
+        raise ValueError("window sums may exceed 2^24: not exact in fp32")
+    cost = np.full((H, W, D), np.inf, np.float32)
+    y, x = np.arange(H), np.arange(W)
+    r0, r1 = np.maximum(y - k, 0), np.maximum(np.minimum(y + k, H), np.maximum(y - k, 0))
+
+    def work(d):
+        diff = L[:, d:] - R[:, :W - d]                 # column c = d .. W-1 at index c - d
+        I = np.zeros((H + 1, W - d + 1), np.int64)
+        np.cumsum(np.cumsum(diff * diff, axis=0), axis=1, out=I[1:, 1:])
+        xs = x[d:]
+        a = np.maximum(xs - k, d) - d                  # src/ssd.cu:40-41
+        b = np.maximum(np.minimum(xs + k, W) - d, a)   # src/ssd.cu:42 (empty window -> 0)
+        top, bot = I[r0], I[r1]
+        cost[:, d:, d] = (bot[:, b] - bot[:, a]) - (top[:, b] - top[:, a])
+
+    with ThreadPoolExecutor(threads or default_threads()) as ex:
+        list(ex.map(work, range(min(D, W))))
+    return cost
+
+
+def birchfield_threaded(left, right, max_disparity: int, threads: int | None = None) -> np.ndarray:
+    """Canonical birchfield() over row chunks on a thread pool (scanlines are independent)."""
+    from concurrent.futures import ThreadPoolExecutor
+    left, right = _f32(left), _f32(right)
+    H, W = left.shape
+    cost = np.empty((H, W, max_disparity), np.float32)
+
+    def work(ab):
+        a, b = ab
+        birchfield(left[a:b], right[a:b], max_disparity, out=cost[a:b])
+
+    with ThreadPoolExecutor(threads or default_threads()) as ex:
+        list(ex.map(work, _row_chunks(H, (threads or default_threads()) * 4)))
+    return cost
+
+
 def birchfield(left, right, max_disparity: int, fill_inf: bool = True,
                cpu_functor: bool = False, out: np.ndarray | None = None) -> np.ndarray:
     """Canonical (reference CUDA functor) semantics; cpu_functor=True reproduces the

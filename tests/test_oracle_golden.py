@@ -98,3 +98,28 @@ def test_path_set_multiplicities():
             exp5[c == cs] = -cs
         assert np.array_equal(cnt[5], exp5), (H, W)
         assert np.array_equal(cnt[7], exp7), (H, W)
+
+
+@pytest.mark.parametrize("H,W,D,k", [(37, 53, 32, 7), (20, 45, 64, 3), (9, 11, 5, 2), (16, 33, 32, 0),
+                                      (30, 20, 40, 7), (5, 3, 8, 7)])
+def test_fast_oracle_forms_equal_the_literal_restatement(H, W, D, k):
+    """The forms the full-size GPU tests use (tests/test_gpu_named_shapes.py) are the pinned
+    restatement, only faster: row chunks on threads (bit-identical by construction: output
+    row y reads image rows [y-k, y+k) only) and, for integer-valued images, int64 integral
+    images (bit-identical because every fp32 partial sum is an exact integer < 2^24)."""
+    from oracle import synth
+    l, r, _ = synth.random_dot_pair(H, W, D, seed=H + W, scale="raw")
+    want = O.ssd(l, r, D, k)
+    assert np.array_equal(O.ssd_exact_int(l, r, D, k, threads=3), want)
+    assert np.array_equal(O.ssd_threaded(l, r, D, k, threads=3), want)
+    lu, ru, _ = synth.random_dot_pair(H, W, D, seed=H + W, scale="unit")
+    assert np.array_equal(O.ssd_threaded(lu, ru, D, k, threads=5), O.ssd(lu, ru, D, k))
+    assert np.array_equal(O.birchfield_threaded(lu, ru, D, threads=5), O.birchfield(lu, ru, D))
+    with pytest.raises(ValueError):
+        O.ssd_exact_int(lu, ru, D, k)           # not integer-valued
+
+
+def test_fast_ssd_equals_the_golden_reference_output(golden):
+    g = golden("cost_raw_24x40x16")
+    assert np.array_equal(O.ssd_exact_int(g["left"], g["right"], 16, 7), g["ssd7"])
+    assert np.array_equal(O.ssd_exact_int(g["left"], g["right"], 16, 3), g["ssd3"])

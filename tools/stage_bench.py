@@ -16,12 +16,17 @@ ap = argparse.ArgumentParser()
 ap.add_argument("shape", nargs="*", type=int, default=[1080, 1920, 128])
 ap.add_argument("--stages", default="ssd,bt,sgm,wta,dp")
 ap.add_argument("--reps", type=int, default=10)
+ap.add_argument("--warm", type=int, default=3)
 a = ap.parse_args()
 H, W, D = a.shape
 left, right, _ = synth.random_dot_pair(H, W, D, seed=1000, scale="raw")
 l, r = torch.from_numpy(left).cuda(), torch.from_numpy(right).cuda()
 N = H * W * D
-peak = 6550.1
+import json as _json
+try:
+    peak = float(_json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["hbm_gbs"])
+except Exception:
+    peak = 6573.2
 algo = {"ssd": 4 * N + 8 * H * W, "bt": 4 * N + 8 * H * W, "sgm": 8 * N + 4 * H * W,
         "wta": 4 * N + 4 * H * W, "dp": 5 * N + 5 * H * W + 8 * H * D}
 ssd, bt = stereomatch.cost.SSD(D), stereomatch.cost.Birchfield(D)
@@ -37,7 +42,7 @@ for name in a.stages.split(","):
     fn = fns[name]
     if name == "wta":
         sgm(cost, l, agg)
-    for _ in range(3):
+    for _ in range(a.warm):
         fn()
     torch.cuda.synchronize()
     ts = []
