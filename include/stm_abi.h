@@ -144,6 +144,42 @@ int stm_pipeline_host_f32(const float *left, const float *right, int32_t *dispar
                           float penalty1, float penalty2, unsigned sgm_flags, int reducer,
                           unsigned dp_flags);
 
+/* ---- CUDA texture objects as SSD inputs (the reference's CUDATexture class and the
+ * compute_ssd(CUDATexture, CUDATexture, cost, k) overload) ------------------ */
+#define STM_TEX_F32 0
+#define STM_TEX_U8 1
+typedef struct stm_texture stm_texture; /* opaque: a cudaArray + cudaTextureObject_t */
+
+/* Replaces CUDATexture.copy_from_tensor(tensor[H,W,C], normalized_coords)
+ * (reference src/cuda_texture.cpp:23-131): `data` is a contiguous [H, W, channels] image of
+ * float32 (STM_TEX_F32) or uint8 (STM_TEX_U8) in host or device memory (data_on_device); 1, 2 or
+ * 4 channels; point filter, clamp addressing, element-type reads, as the reference.  Normalized
+ * coordinates need power-of-two sizes.  Synchronous (allocates a cudaArray and copies). */
+int stm_texture_create(const void *data, int data_on_device, int H, int W, int channels, int dtype,
+                       int normalized_coords, stm_texture **out);
+/* Replaces CUDATexture.release() (src/cuda_texture.cpp:12-21).  NULL is a no-op. */
+int stm_texture_destroy(stm_texture *texture);
+/* The read-only attributes of the reference class (src/cuda_texture.cpp:177-186): height, width,
+ * channels, dtype, use_normalized_coords, cuda_texture_object.  Any output pointer may be NULL. */
+int stm_texture_info(const stm_texture *texture, int *H, int *W, int *channels, int *dtype,
+                     int *normalized_coords, unsigned long long *cuda_texture_object);
+/* Replaces CUDATexture.to_tensor() (src/cuda_texture.cpp:133-165): copies the texels to a HOST
+ * buffer [H, W, channels] of the texture's dtype (the reference always returns a float32 host
+ * tensor, which is wrong for uint8 textures; here the dtype is the texture's).  Synchronous. */
+int stm_texture_to_host(const stm_texture *texture, void *dst);
+/* Replaces CUDATexture._run_transfer_test_kernel(texture, out) (src/cuda_texture_gpu.cu:9-49):
+ * a kernel reads every texel with tex2D at (col, row) and writes channel 0 to the DEVICE image
+ * out[H, W] of the texture's dtype (out_dtype must match).  Enqueued on `stream`. */
+int stm_texture_read(const stm_texture *texture, void *out, int out_dtype, void *stream);
+/* Replaces CostOps.compute_ssd(CUDATexture, CUDATexture, cost_volume, kernel_size)
+ * (reference src/cost.cpp:10-13 -> CostOps::ComputeSSD, src/ssd.cu:137-153; kernel :83-135).  Same
+ * values as stm_ssd_f32 on the images the textures hold.  Both textures float32, unnormalized,
+ * same size; cost is a DEVICE volume [H, W, D].  `scratch`: stm_ssd_tex_scratch_bytes(H, W) bytes of
+ * device memory (every texel is fetched once into it, then the tiled SSD kernel runs). */
+size_t stm_ssd_tex_scratch_bytes(int H, int W);
+int stm_ssd_tex_f32(const stm_texture *left, const stm_texture *right, float *cost, int D,
+                    int kernel_size, void *scratch, size_t scratch_bytes, void *stream);
+
 /* Number of kernel launches the library has enqueued in this process (bench "gpu_launches"). */
 unsigned long long stm_launch_count(void);
 

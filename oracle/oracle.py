@@ -170,13 +170,16 @@ def sgm_visit_counts(H: int, W: int) -> np.ndarray:
 
 
 def sgm(cost, left, penalty1: float = 0.1, penalty2: float = 0.2,
-        min_over_all_d: bool = False, out: np.ndarray | None = None) -> np.ndarray:
+        min_over_all_d: bool = False, out: np.ndarray | None = None,
+        directions: int = 0xff) -> np.ndarray:
+    """directions: bit i keeps the directed paths of direction i (order of sgm_visit_counts);
+    0xff is the reference's whole aggregation."""
     cost, left = _f32(cost), _f32(left)
     H, W, D = cost.shape
     out = np.zeros_like(cost) if out is None else out
-    lib().stm_oracle_sgm(_p(cost), _p(left), _p(out), H, W, D,
-                         ctypes.c_float(penalty1), ctypes.c_float(penalty2),
-                         int(min_over_all_d))
+    lib().stm_oracle_sgm_dirs(_p(cost), _p(left), _p(out), H, W, D,
+                              ctypes.c_float(penalty1), ctypes.c_float(penalty2),
+                              int(min_over_all_d), ctypes.c_uint(directions))
     return out
 
 

@@ -24,6 +24,7 @@ STM_SGM_FUSED_SWEEPS = 4
 STM_SGM_DISPARITY_ONLY = 8
 STM_SGM_SEQUENTIAL = 16
 STM_DP_CPU_EXACT = 1
+STM_TEX_F32, STM_TEX_U8 = 0, 1
 
 if not _LIB_PATH.exists():
     raise ImportError(
@@ -47,8 +48,18 @@ _lib.stm_dp_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _u, _vp]
 _lib.stm_sgm_pass_timing.argtypes = [_i]
 _lib.stm_sgm_last_pass_ms.argtypes = [_vp, _vp, _i]
 _lib.stm_pipeline_host_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _u, _i, _u]
+_pp = ctypes.POINTER
+_lib.stm_texture_create.argtypes = [_vp, _i, _i, _i, _i, _i, _i, _pp(_vp)]
+_lib.stm_texture_destroy.argtypes = [_vp]
+_lib.stm_texture_info.argtypes = [_vp, _pp(_i), _pp(_i), _pp(_i), _pp(_i), _pp(_i), _pp(ctypes.c_ulonglong)]
+_lib.stm_texture_to_host.argtypes = [_vp, _vp]
+_lib.stm_texture_read.argtypes = [_vp, _vp, _i, _vp]
+_lib.stm_ssd_tex_scratch_bytes.argtypes = [_i, _i]
+_lib.stm_ssd_tex_scratch_bytes.restype = _sz
+_lib.stm_ssd_tex_f32.argtypes = [_vp, _vp, _vp, _i, _i, _vp, _sz, _vp]
 for _name in ("stm_ssd_f32", "stm_birchfield_f32", "stm_sgm_f32", "stm_sgm_wta_f32", "stm_wta_f32",
-              "stm_dp_f32", "stm_pipeline_host_f32"):
+              "stm_dp_f32", "stm_pipeline_host_f32", "stm_texture_create", "stm_texture_destroy",
+              "stm_texture_info", "stm_texture_to_host", "stm_texture_read", "stm_ssd_tex_f32"):
     getattr(_lib, _name).restype = _i
 
 
@@ -106,13 +117,128 @@ def _sgm_workspace(device: torch.device, nbytes: int) -> torch.Tensor:
     return ws
 
 
+class CUDATexture:
+    """reference src/cuda_texture.cpp:167-192 (pybind class `CUDATexture`): a cudaArray + CUDA texture
+    object holding an [H, W, C] float32 / uint8 image (C in 1, 2, 4; point filter, clamp).  Same
+    methods and read-only attributes; the handle is owned by libstm_b200 (stm_texture_*)."""
+
+    _DTYPES = {torch.float32: STM_TEX_F32, torch.uint8: STM_TEX_U8}
+
+    def __init__(self):
+        self._handle = None
+        self._device = None
+        self.width = 0
+        self.height = 0
+        self.channels = 0
+        self.dtype = torch.float32
+        self.cuda_texture_object = 0
+        self.use_normalized_coords = False
+
+    def is_empty(self) -> bool:
+        return self._handle is None
+
+    def copy_from_tensor(self, tensor: torch.Tensor, normalized_coords: bool = False) -> None:
+        """tensor: [H, W, C] float32 / uint8, on the host or on a CUDA device."""
+        if not self.is_empty():
+            raise RuntimeError("CUDATExture::CopyFromTensor: Loading into a non-empty instance.")
+        if tensor.dim() != 3:
+            raise RuntimeError("CUDATExture::CopyFromTensor: expected a [H, W, C] tensor")
+        if tensor.dtype not in self._DTYPES:
+            raise RuntimeError("CUDATExture::CopyFromTensor: Input tensor's dtype not supported.")
+        tensor = tensor.contiguous()
+        H, W, C = tensor.shape
+        # reference src/cuda_texture.cpp:29-50, checked before any CUDA call
+        if normalized_coords and ((H & (H - 1)) or (W & (W - 1))):
+            raise RuntimeError("CUDATExture::CopyFromTensor: Only power of 2 texture can use "
+                               "normalized coordinates")
+        if C == 3:
+            raise RuntimeError("CUDATExture::CopyFromTensor: Tensor with 3 or more than 4 channels "
+                               "aren't supported")
+        if C < 1 or C > 4:
+            raise RuntimeError("CUDATExture::CopyFromTensor: Tensor with more than 4 channels aren't "
+                               "supported")
+        if not torch.cuda.is_available():
+            raise RuntimeError("CUDATexture needs a CUDA device (stereomatch_b200 has no CPU fallback)")
+        device = tensor.device if tensor.is_cuda else torch.device("cuda", torch.cuda.current_device())
+        handle = _vp()
+        with torch.cuda.device(device):
+            if tensor.is_cuda:
+                torch.cuda.current_stream().synchronize()   # the copy below is not stream-ordered
+            _check(_lib.stm_texture_create(tensor.data_ptr(), int(tensor.is_cuda), H, W, C,
+                                           self._DTYPES[tensor.dtype], int(bool(normalized_coords)),
+                                           ctypes.byref(handle)))
+        self._handle, self._device = handle, device
+        self.width, self.height, self.channels, self.dtype = W, H, C, tensor.dtype
+        obj = ctypes.c_ulonglong()
+        _check(_lib.stm_texture_info(handle, None, None, None, None, None, ctypes.byref(obj)))
+        self.cuda_texture_object = int(obj.value)
+        self.use_normalized_coords = bool(normalized_coords)
+
+    def to_tensor(self) -> torch.Tensor:
+        """[H, W, C] HOST tensor of the texture's dtype (the reference returns a host tensor too)."""
+        if self.is_empty():
+            raise RuntimeError("CUDATexture::ToTensor: empty texture")
+        out = torch.empty(self.height, self.width, self.channels, dtype=self.dtype)
+        with torch.cuda.device(self._device):
+            _check(_lib.stm_texture_to_host(self._handle, out.data_ptr()))
+        return out
+
+    def release(self) -> None:
+        if self._handle is not None:
+            handle, self._handle = self._handle, None
+            self.cuda_texture_object = 0
+            _check(_lib.stm_texture_destroy(handle))
+
+    @staticmethod
+    def _run_transfer_test_kernel(input_texture: "CUDATexture", output_tensor: torch.Tensor) -> None:
+        """reference src/cuda_texture_gpu.cu:29-49: a kernel reads every texel through tex2D and
+        writes it to `output_tensor` ([H, W], the texture's dtype, CUDA)."""
+        if not output_tensor.is_cuda:
+            raise RuntimeError("Cost volume must be a CUDA tensor.")
+        if output_tensor.dtype not in CUDATexture._DTYPES:
+            raise RuntimeError("Cannot test this type")
+        if input_texture.is_empty():
+            raise RuntimeError("_run_transfer_test_kernel: empty texture")
+        if tuple(output_tensor.shape) != (input_texture.height, input_texture.width):
+            raise RuntimeError("_run_transfer_test_kernel: output shape must be [H, W]")
+        _out("output_tensor", output_tensor)
+        with torch.cuda.device(output_tensor.device):
+            _check(_lib.stm_texture_read(input_texture._handle, output_tensor.data_ptr(),
+                                         CUDATexture._DTYPES[output_tensor.dtype], _stream()))
+            torch.cuda.current_stream().synchronize()     # the reference synchronises the device here
+
+    @staticmethod
+    def _run_binding_test_kernel(input_tensor: torch.Tensor, output_tensor: torch.Tensor) -> None:
+        """reference src/cuda_texture_gpu.cu:69-110: tensor -> temporary texture -> tensor."""
+        tex = CUDATexture()
+        tex.copy_from_tensor(input_tensor.reshape(input_tensor.size(0), input_tensor.size(1), 1).float())
+        try:
+            CUDATexture._run_transfer_test_kernel(tex, output_tensor)
+        finally:
+            tex.release()
+
+
+_tex_scratch = {}
+
+
+def _ssd_tex_scratch(device: torch.device, nbytes: int) -> torch.Tensor:
+    with torch.cuda.device(device):
+        key = (device, _stream())
+    ws = _tex_scratch.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _tex_scratch[key] = ws
+    return ws
+
+
 class CostOps:
     """reference include/stereomatch/cost.hpp:8-20"""
 
     @staticmethod
     def compute_ssd(left_image, right_image, cost_volume, kernel_size: int) -> None:
-        if not isinstance(left_image, torch.Tensor):
-            raise RuntimeError("compute_ssd(CUDATexture, ...) is not part of the B200 hot path")
+        if isinstance(left_image, CUDATexture) or isinstance(right_image, CUDATexture):
+            # the reference's second overload (src/cost.cpp:10-13)
+            return CostOps._compute_ssd_texture(left_image, right_image, cost_volume, kernel_size)
         left = _gpu("SSDKernel: left_image", left_image, torch.float32, 2)
         right = _gpu("SSDKernel: right_image", right_image, torch.float32, 2, left)
         cost = _out("cost_volume", _gpu("SSDKernel: cost_volume", cost_volume, torch.float32, 3, left))
@@ -123,6 +249,26 @@ class CostOps:
         with torch.cuda.device(left.device):
             _check(_lib.stm_ssd_f32(left.data_ptr(), right.data_ptr(), cost.data_ptr(), H, W,
                                     cost.shape[2], int(kernel_size), _stream()))
+
+    @staticmethod
+    def _compute_ssd_texture(left_image, right_image, cost_volume, kernel_size: int) -> None:
+        if not (isinstance(left_image, CUDATexture) and isinstance(right_image, CUDATexture)):
+            raise TypeError("compute_ssd: both images must be CUDATexture (or both tensors)")
+        if left_image.is_empty() or right_image.is_empty():
+            raise RuntimeError("compute_ssd: empty texture")
+        if not cost_volume.is_cuda:
+            raise RuntimeError("Cost volume must be a CUDA tensor.")  # reference src/ssd.cu:140-142
+        cost = _out("cost_volume", _gpu("SSDKernel: cost_volume", cost_volume, torch.float32, 3))
+        if cost.device != left_image._device or cost.device != right_image._device:
+            raise RuntimeError("Check failed: SSDKernel: textures and cost volume must be on the same device")
+        H, W = left_image.height, left_image.width
+        if tuple(cost.shape[:2]) != (H, W):
+            raise RuntimeError("SSDKernel: texture / cost volume shapes do not match")
+        nbytes = int(_lib.stm_ssd_tex_scratch_bytes(H, W))
+        ws = _ssd_tex_scratch(cost.device, nbytes)
+        with torch.cuda.device(cost.device):
+            _check(_lib.stm_ssd_tex_f32(left_image._handle, right_image._handle, cost.data_ptr(),
+                                        cost.shape[2], int(kernel_size), ws.data_ptr(), ws.numel(), _stream()))
 
     @staticmethod
     def compute_birchfield(left_image, right_image, cost_volume, kernel_size: int = 4) -> None:

@@ -1,18 +1,12 @@
 """String tables and `create_pipeline` for the command-line callers of the path
 (interface of reference stereomatch/cli_common.py:9-52: same keys, same argument order)."""
 from .aggregation import Semiglobal
-from .cost import SSD, Birchfield
+from .cost import SSD, SSDTexture, Birchfield
 from .disparity_reduce import DynamicProgramming, WinnerTakesAll
 from .pipeline import Pipeline
 
 
-def _no_texture(_max_disparity):
-    # reference cli_common.py:11 maps "ssd-texture" to SSDTexture (CUDA texture objects,
-    # SURVEY.md 8(f) N3); that input path is not provided here, the plain SSD kernel is.
-    raise RuntimeError("cost method 'ssd-texture' is not provided by stereomatch_b200; use 'ssd'")
-
-
-COST_METHODS = {"ssd": SSD, "ssd-texture": _no_texture, "birchfield": Birchfield}
+COST_METHODS = {"ssd": SSD, "ssd-texture": SSDTexture, "birchfield": Birchfield}
 AGGREGATION_METHODS = {"sgm": Semiglobal}
 DISPARITY_METHODS = {"wta": WinnerTakesAll, "dyn": DynamicProgramming}
 

@@ -5,6 +5,7 @@ import torch
 
 from ._common import empty_tensor
 from ._cstereomatch import CostOps as _CostOps
+from .cuda_texture import CUDATexture
 
 
 class SSD:
@@ -27,6 +28,26 @@ class SSD:
         (+inf where d > x)."""
         cost_volume = empty_tensor(left_image.size(0), left_image.size(1), self.max_disparity,
                                    dtype=self.cost_volume_dtype, device=left_image.device,
+                                   reuse_tensor=cost_volume)
+        _CostOps.compute_ssd(left_image, right_image, cost_volume, self.kernel_size)
+        return cost_volume
+
+
+class SSDTexture:
+    """SSD over CUDA texture inputs (reference stereomatch/cost.py:51-77): same volume as SSD on
+    the images the textures hold.  Float32, unnormalised textures of equal size."""
+
+    def __init__(self, max_disparity: int, kernel_size: int = 7):
+        self.max_disparity = max_disparity
+        self.kernel_size = kernel_size
+
+    def __call__(self, left_image: CUDATexture, right_image: CUDATexture,
+                 cost_volume: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if left_image.use_normalized_coords or right_image.use_normalized_coords:
+            raise RuntimeError("Texture coordinates can't be normalized for this implementation")
+        # the reference hard-codes cuda:0 (cost.py:72); here the volume goes where the texture is
+        cost_volume = empty_tensor(left_image.height, left_image.width, self.max_disparity,
+                                   dtype=torch.float32, device=left_image._device,
                                    reuse_tensor=cost_volume)
         _CostOps.compute_ssd(left_image, right_image, cost_volume, self.kernel_size)
         return cost_volume

@@ -4,11 +4,26 @@ from typing import Callable, Optional
 import torch
 
 from .aggregation import Semiglobal
+from .cost import SSDTexture
+from .cuda_texture import CUDATexture
 from .disparity_reduce import WinnerTakesAll
 
 CostFunction = Callable[[torch.Tensor, torch.Tensor, torch.Tensor], torch.Tensor]
 AggregationFunction = Callable[[torch.Tensor, torch.Tensor, torch.Tensor], torch.Tensor]
 DisparityReduceFunction = Callable[[torch.Tensor, torch.Tensor], torch.Tensor]
+
+
+class _TexCostFunctionWrapper:
+    """Lets Pipeline.estimate take tensors when the cost function wants textures
+    (reference stereomatch/pipeline.py:22-33): both images are loaded into new textures per call."""
+
+    def __init__(self, cost_function):
+        self.cost_function = cost_function
+
+    def __call__(self, left_image: torch.Tensor, right_image: torch.Tensor, cost_volume: torch.Tensor):
+        return self.cost_function(CUDATexture.from_tensor(left_image.cuda()),
+                                  CUDATexture.from_tensor(right_image.cuda()),
+                                  cost_volume=cost_volume)
 
 
 class Pipeline:
@@ -17,7 +32,7 @@ class Pipeline:
 
     def __init__(self, cost: CostFunction, disparity_reduce: DisparityReduceFunction,
                  aggregation: Optional[AggregationFunction] = None):
-        self.cost = cost
+        self.cost = _TexCostFunctionWrapper(cost) if isinstance(cost, SSDTexture) else cost
         self.disparity_reduce = disparity_reduce
         self.aggregation = aggregation
         self._cost_volume = None

@@ -33,8 +33,9 @@ def test_create_pipeline_builds_the_named_stages(sm):
     assert create_pipeline("ssd", "wta", "no-such-aggregation").aggregation is None   # .get(), :46
     with pytest.raises(KeyError):
         create_pipeline("census", "wta", None)
-    with pytest.raises(RuntimeError, match="ssd-texture"):
-        create_pipeline("ssd-texture", "wta", None)
+    t = create_pipeline("ssd-texture", "wta", None)     # cli_common.py:11; Pipeline wraps it, pipeline.py:54-55
+    assert type(t.cost).__name__ == "_TexCostFunctionWrapper"
+    assert type(t.cost.cost_function) is sm.cost.SSDTexture and t.cost.cost_function.max_disparity == 32
 
 
 @pytest.mark.parametrize("ext", ["png", "pgm"])

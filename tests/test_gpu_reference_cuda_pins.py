@@ -95,28 +95,73 @@ def test_birchfield_equals_reference_cuda_kernel(sm, H, W, D, scale):
 
 
 # ------------------------------------------------------------------------------------ SGM
-@pytest.mark.parametrize("H,W,D", [(48, 48, 32), (40, 72, 64), (60, 100, 128), (96, 64, 32), (375, 450, 64)])
-def test_sgm_min_over_all_d_against_reference_cuda_kernel(sm, H, W, D):
-    """STM_SGM_MIN_ALL_D (K = {0..D-1}) is the reference CUDA kernel's rule.  That kernel loses
-    `+=` updates when two blocks hit a pixel together (F7), which only ever makes an entry
-    SMALLER by one direction's term, so: the bulk of the finite entries agree to 1e-4, no entry
-    of the reference exceeds ours beyond the bar, and with K = {0..D-2} (the CPU reference's
-    rule) the agreement is measurably worse wherever the minimum sits at d = D-1."""
+def _subset_sum_match(ref, terms, want, rtol=1e-4, chunk=1 << 16):
+    """For every finite entry: does `ref` equal the sum of SOME subset of the eight per-direction
+    terms (within rtol of the full sum)?  Returns (matches, number of terms lost) per entry."""
+    fin = np.isfinite(want)
+    r, w = ref[fin].astype(np.float64), want[fin].astype(np.float64)
+    t = np.stack([x[fin] for x in terms]).astype(np.float64)                 # [8, N]
+    masks = ((np.arange(256)[:, None] >> np.arange(8)[None, :]) & 1).astype(np.float64)   # [256, 8]
+    ok = np.zeros(r.shape, bool)
+    lost = np.full(r.shape, 99, np.int64)
+    nlost = 8 - masks.sum(1).astype(np.int64)
+    for a in range(0, r.size, chunk):
+        cand = masks @ t[:, a:a + chunk]                                      # [256, n]
+        hit = np.abs(cand - r[a:a + chunk][None]) <= rtol * np.maximum(np.abs(w[a:a + chunk]), 1e-30)[None]
+        ok[a:a + chunk] = hit.any(0)
+        lost[a:a + chunk] = np.where(hit, nlost[:, None], 99).min(0)
+    return ok, lost
+
+
+@pytest.mark.parametrize("H,W,D", [(48, 48, 32), (64, 64, 64), (40, 40, 128)])
+def test_sgm_min_over_all_d_terms_against_reference_cuda_kernel(sm, H, W, D):
+    """STM_SGM_MIN_ALL_D (K = {0..D-1}) is the reference CUDA kernel's rule
+    (src/semiglobal_gpu.cu:70-81).  That kernel accumulates the directions of one launch with a
+    non-atomic `+=` from different blocks (:62,:97), and the blocks of the three directions with
+    the same vertical component reach a pixel at the same step, so MOST entries lose one or two
+    terms (measured rates are printed).  What can be pinned, and is: every entry the
+    reference CUDA kernel produces is the sum of a SUBSET of the eight per-direction terms of the
+    restatement O.sgm(min_over_all_d=True) -- never more, never anything else -- and the entries
+    that lost nothing equal the product kernel's sums to 1e-4.  Square shapes: every directed path
+    runs exactly once (no corner-diagonal replays), so the terms are the oracle's one-direction runs."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 7 + W, scale="unit")
     cost = O.ssd(left, right, D, 3)
     ref = ref_ops.sgm(cost, left, 0.1, 0.2, device="cuda")
     want = O.sgm(cost, left, 0.1, 0.2, min_over_all_d=True)
     got = sm.aggregation.Semiglobal(0.1, 0.2, min_over_all_d=True)(cuda(cost), cuda(left)).cpu().numpy()
     fin = np.isfinite(want)
-    assert np.array_equal(np.isfinite(got), fin)
+    assert np.array_equal(np.isfinite(got), fin) and np.array_equal(np.isfinite(ref), fin)
     den = np.maximum(np.abs(want[fin]), 1e-30)
     assert (np.abs(got[fin] - want[fin]) / den).max() <= 1e-4        # product == restatement
+    terms = [O.sgm(cost, left, 0.1, 0.2, min_over_all_d=True, directions=1 << d) for d in range(8)]
+    ok, lost = _subset_sum_match(ref, terms, want)
+    rate = {k: float((lost == k).mean()) for k in range(0, 5)}
+    print(f"SGM MIN_ALL_D {H}x{W}x{D} vs reference CUDA: entries that are a subset sum {ok.mean():.6f}; "
+          f"terms lost 0/1/2/3/4: " + " ".join(f"{rate[k]:.3f}" for k in range(5)))
+    assert ok.all()                                  # nothing but sub-sums of the restatement's terms
+    assert (ref[fin] <= want[fin] * (1 + 1e-4) + 1e-30).all()        # a lost update only removes a term
+    intact = lost == 0
+    assert intact.any()
+    assert (np.abs(got[fin][intact] - ref[fin][intact]) / den[intact]).max() <= 1e-4
+    # the other rule (K = {0..D-2}, the compiled CPU reference) is a different function: the same
+    # check against ITS terms fails somewhere whenever a running minimum sits at d = D-1
+    terms_cpu = [O.sgm(cost, left, 0.1, 0.2, directions=1 << d) for d in range(8)]
+    if any(not np.array_equal(a, b) for a, b in zip(terms, terms_cpu)):
+        ok_cpu, _ = _subset_sum_match(ref, terms_cpu, O.sgm(cost, left, 0.1, 0.2))
+        print(f"   with the CPU rule's terms instead: {ok_cpu.mean():.6f}")
+
+
+@pytest.mark.parametrize("H,W,D", [(40, 72, 64), (96, 64, 32), (375, 450, 64)])
+def test_sgm_reference_cuda_kernel_never_exceeds_the_restatement(sm, H, W, D):
+    """Landscape / portrait (corner-diagonal replays, F5): the reference CUDA result is bounded
+    by the restatement entry by entry (lost updates only remove terms); agreement rate printed."""
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 7 + W, scale="unit")
+    cost = O.ssd_threaded(left, right, D, 3)
+    ref = ref_ops.sgm(cost, left, 0.1, 0.2, device="cuda")
+    want = O.sgm(cost, left, 0.1, 0.2, min_over_all_d=True)
+    fin = np.isfinite(want)
     assert np.array_equal(np.isfinite(ref), fin)
-    rel = (ref[fin] - want[fin]) / den
-    agree = float((np.abs(rel) <= 1e-4).mean())
-    lost = float((rel < -1e-4).mean())
-    above = float((rel > 1e-4).mean())
-    print(f"SGM MIN_ALL_D {H}x{W}x{D} vs reference CUDA: agree {agree:.5f}, lost updates {lost:.2e}, "
-          f"above {above:.2e}")
-    assert above == 0.0          # a lost update can only remove a term
-    assert agree >= 0.90         # allowance for the reference's race (measured rate is printed)
+    rel = (ref[fin] - want[fin]) / np.maximum(np.abs(want[fin]), 1e-30)
+    print(f"SGM MIN_ALL_D {H}x{W}x{D} vs reference CUDA: agree {(np.abs(rel) <= 1e-4).mean():.4f}, "
+          f"lost updates {(rel < -1e-4).mean():.4f}")
+    assert (rel <= 1e-4).all()
