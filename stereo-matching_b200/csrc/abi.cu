@@ -55,6 +55,16 @@ struct HostPipelineScratch {
       cap[i] = 0;
     }
   }
+  // thread exit: give the scratch back (errors ignored: at process exit the context may be gone)
+  ~HostPipelineScratch() {
+    if (device < 0) return;
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess) { cudaGetLastError(); return; }
+    if (cur != device && cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return; }
+    reset();
+    if (cur != device) cudaSetDevice(cur);
+    cudaGetLastError();
+  }
 };
 
 }  // namespace stm

@@ -16,6 +16,8 @@
 // come from two rotating shuffles per vector, min_k from one redux.sync on
 // order-preserving integer keys.  The next pixel's cost vector is prefetched while the
 // current one is being reduced.
+#include <mutex>
+
 #include "lanevec.cuh"
 #include <cstdlib>
 #include <cstring>
@@ -287,8 +289,10 @@ __global__ void sgm_repeat_add_kernel(float *__restrict__ out, const float *__re
 // Warps of one kernel variant that can be resident on the whole GPU at once (occupancy API).
 template <int NV, int VW, bool ACC, bool WTA, int PFSEL>
 static int resident_warps() {
-  static int cached = -1;  // per instantiation; a race would only recompute the same value
-  if (cached < 0) {
+  static PerDeviceInt cache;  // per instantiation and device; a race recomputes the same value
+  const int dev = device_slot();
+  int cached = 0;
+  if (!cache.get(dev, &cached)) {
     int nb = 0;
     const int threads = SgmPf<NV, VW, PFSEL>::kThreads;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
@@ -297,6 +301,7 @@ static int resident_warps() {
       nb = 0;
     }
     cached = nb * (threads / 32) * num_sms();
+    cache.set(dev, cached);
   }
   return cached;
 }
@@ -347,8 +352,10 @@ static int pfsel_override(int dir) {
 // Row-synchronous diagonal pass (sgm_diag_rows_kernel): W slots; `busy` of them do H steps.
 template <int NV, int VW, int PFSEL>
 static int diag_rows_resident() {
-  static int cached = -1;
-  if (cached < 0) {
+  static PerDeviceInt cache;
+  const int dev = device_slot();
+  int cached = 0;
+  if (!cache.get(dev, &cached)) {
     int nb = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, sgm_diag_rows_kernel<NV, VW, PFSEL>,
                                                       SgmPf<NV, VW, PFSEL>::kThreads, 0) != cudaSuccess) {
@@ -356,6 +363,7 @@ static int diag_rows_resident() {
       nb = 0;
     }
     cached = nb * (SgmPf<NV, VW, PFSEL>::kThreads / 32) * num_sms();
+    cache.set(dev, cached);
   }
   return cached;
 }
@@ -692,18 +700,26 @@ __global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict
 
 // Helper streams and events, one set per device ordinal (a process normally drives one GPU,
 // but streams and events belong to the device that was current when they were created).
-constexpr int kMaxDevices = 16;
+// Threading: the fork event, the seven helper streams and the join events of a device are shared by
+// every caller on that device, so the whole fork ... join ENQUEUE sequence of one call runs under
+// the set's mutex (another host thread could otherwise re-record `fork` between this call's record
+// and its helper streams' waits).  cudaStreamWaitEvent captures the event's state when it is
+// called, so once the sequence has been enqueued the next caller may reuse the events.  Calls from
+// several threads / streams on one device are therefore correct and share the helper streams.
 struct AuxStreams {
+  std::mutex mu;
   cudaStream_t stream[7];
   cudaEvent_t fork, join[7];
   bool ready = false;
 };
 static AuxStreams g_aux[kMaxDevices];
+// Returns the current device's set; the caller must hold a->mu while it uses it.
 static int aux_streams(AuxStreams **out) {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices)
     return fail(STM_ECUDA, "sgm: unsupported device ordinal");
   AuxStreams &a = g_aux[dev];
+  std::lock_guard<std::mutex> init_lock(a.mu);
   if (!a.ready) {
     if (cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: cudaEventCreate failed");
@@ -727,6 +743,7 @@ static int sgm_concurrent(const float *cost, const float *image, float *out, int
   AuxStreams *aux = nullptr;
   int rc = aux_streams(&aux);
   if (rc) return rc;
+  std::lock_guard<std::mutex> enqueue_lock(aux->mu);  // fork ... join is one critical section
   const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
   const size_t N = (size_t)H * W * D;
   if (cudaEventRecord(aux->fork, stream) != cudaSuccess)

@@ -207,8 +207,10 @@ static int run_sgm_row(const float *cost, const float *image, float *out, int H,
                        float p1, float p2, int dir, int min_limit, bool acc, cudaStream_t stream) {
   using C = rowk::Cfg<NV, VW>;
   if (C::kDpad != D) return 1;  // padded lane maps (D % 32 != 0) stay on the generic kernel
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceInt configured;  // the > 48 KB opt-in is per function AND per device
+  const int dev = device_slot();
+  int done = 0;
+  if (!configured.get(dev, &done)) {
     cudaError_t e = cudaSuccess;
 #define STM_ROW_ATTR(A_, B_)                                                                  \
   if (e == cudaSuccess)                                                                      \
@@ -221,7 +223,7 @@ static int run_sgm_row(const float *cost, const float *image, float *out, int H,
       cudaGetLastError();
       return 1;
     }
-    configured = true;
+    configured.set(dev, 1);
   }
   const int blocks = (H + rowk::kWarps - 1) / rowk::kWarps;
   const dim3 grid(blocks), block(rowk::kWarps * 32);

@@ -694,8 +694,10 @@ static const void *sweep_kernel(bool up, bool wta) {
 template <int NV, int VW>
 static int ctas(int W) {
   using C = Cfg<NV * 32 * VW>;
-  static int cap = -1;  // per instantiation
-  if (cap < 0) {
+  static PerDeviceInt cache;  // per instantiation and device (attribute opt-in + occupancy)
+  const int dev = device_slot();
+  int cap = 0;
+  if (!cache.get(dev, &cap)) {
     int per_sm = 1 << 30;
     for (int v = 0; v < 3; ++v) {
       const void *k = sweep_kernel<NV, VW>(v > 0, v > 1);
@@ -708,6 +710,7 @@ static int ctas(int W) {
       per_sm = n < per_sm ? n : per_sm;
     }
     cap = per_sm * num_sms();
+    cache.set(dev, cap);
   }
   int G = cap < kMaxCtas ? cap : kMaxCtas;
   if (G > W / 2) G = W / 2;

@@ -241,14 +241,16 @@ template <int K, int RUNS>
 static int run_ssd_tiled(const float *left, const float *right, float *cost, int H, int W, int D,
                          cudaStream_t stream) {
   using Cfg = SsdCfg<K, RUNS>;
-  static bool configured = false;
-  if (!configured) {
+  static PerDeviceInt configured;  // the > 48 KB opt-in is per function AND per device
+  const int dev = device_slot();
+  int done = 0;
+  if (!configured.get(dev, &done)) {
     if (cudaFuncSetAttribute(ssd_tiled_kernel<K, RUNS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)Cfg::SMEM) != cudaSuccess) {
       cudaGetLastError();
       return 1;  // fall back to the generic kernel
     }
-    configured = true;
+    configured.set(dev, 1);
   }
   const int nx = (W + Cfg::TX - 1) / Cfg::TX;
   const int nd = (D + Cfg::DC - 1) / Cfg::DC;

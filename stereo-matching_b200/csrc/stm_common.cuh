@@ -51,13 +51,38 @@ inline int check_shape(const char *op, int H, int W, int D) {
   return STM_OK;
 }
 
+// Everything cached from a device query or set by cudaFuncSetAttribute is PER DEVICE: one process
+// may drive several GPUs from several host threads.  Caches are arrays indexed by the device
+// ordinal; slots hold value + 1 so that zero-initialised storage means "not yet queried".  Two
+// threads racing on a slot compute the same value (plain int stores; benign).
+constexpr int kMaxDevices = 64;
+inline int device_slot() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) return -1;
+  return dev < kMaxDevices ? dev : -1;  // -1: no slot, the value is recomputed on every call
+}
+struct PerDeviceInt {
+  int slot[kMaxDevices] = {0};
+  bool get(int dev, int *v) const {
+    if (dev < 0 || slot[dev] == 0) return false;
+    *v = slot[dev] - 1;
+    return true;
+  }
+  void set(int dev, int v) {
+    if (dev >= 0) slot[dev] = v + 1;
+  }
+};
+
 inline int num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+  static PerDeviceInt cache;
+  const int dev = device_slot();
+  int n = 0;
+  if (!cache.get(dev, &n)) {
+    int cur = 0;
+    if (cudaGetDevice(&cur) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, cur) != cudaSuccess || n <= 0)
       n = 148;
+    cache.set(dev, n);
   }
   return n;
 }

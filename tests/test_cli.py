@@ -69,7 +69,7 @@ def test_gray_conversion_is_pil_luma(sm, tmp_path):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("opts", [["-cm", "ssd", "-am", "sgm", "-dm", "wta"], ["-cm", "birchfield", "-dm", "dyn"],
-                                  ["-cm", "ssd"]])
+                                  ["-cm", "ssd"], ["-cm", "ssd-texture", "-am", "sgm"]])
 def test_cli_writes_what_the_pipeline_returns(sm, tmp_path, opts):
     from PIL import Image
     from stereomatch import cli_image
@@ -83,4 +83,12 @@ def test_cli_writes_what_the_pipeline_returns(sm, tmp_path, opts):
     ns = cli_image.build_parser().parse_args(["a", "b", str(D), "c"] + opts)
     pipe = create_pipeline(ns.cost_method, ns.disparity_method, ns.aggregation_method, D)
     want = pipe.estimate(torch.from_numpy(left).cuda(), torch.from_numpy(right).cuda()).cpu().numpy()
-    assert np.array_equal(cli_image.read_u16(out), want.astype(np.uint16))
+    got = cli_image.read_u16(out)
+    assert np.array_equal(got, want.astype(np.uint16))
+    # ... and what it writes is the ORACLE's chain on the same files (<= 0.1 % of pixels, north_star)
+    from oracle import oracle as O
+    vol = O.ssd(left, right, D, 7) if ns.cost_method.startswith("ssd") else O.birchfield(left, right, D)
+    if ns.aggregation_method == "sgm":
+        vol = O.sgm(vol, left, 0.1, 0.2)
+    owant = O.wta(vol) if ns.disparity_method == "wta" else O.dp(vol, "cuda")
+    assert float((got.astype(np.int32) != owant).mean()) <= 1e-3
