@@ -115,6 +115,26 @@ int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *d
                     int W, int D, float penalty1, float penalty2, unsigned flags, void *workspace,
                     size_t workspace_bytes, void *stream);
 
+/* Aggregation that allocates NOTHING, in the caller or in the library.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * stm_sgm_f32 with STM_SGM_SEQUENTIAL (the eight direction passes one after the other in the
+ * reference's order, accumulating into `out` unless STM_SGM_OVERWRITE), but the only scratch that
+ * schedule needs -- the corner up-diagonal's L vectors, min(H, W) * padded-D floats -- is a
+ * file-scope `static __device__` array of STM_SGM_STATIC_MAX_FLOATS floats (2 MiB, held by every
+ * GPU that loads the library until exit) instead of a workspace argument.  padded D = D rounded
+ * up to a multiple of 32.  Shapes with min(H, W) * padded D > STM_SGM_STATIC_MAX_FLOATS are
+ * rejected with STM_EINVAL (1080p fits up to D = 480; use stm_sgm_f32 beyond).  Calls no
+ * cudaMalloc / cudaFree / allocating library routine; enqueues on `stream` like the other *_f32
+ * entry points.  flags: STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE.
+ * SHARED STATE: every call on a device uses the same array, and it keeps the last call's contents.
+ * Nothing in it needs to start at zero (each call writes what it later reads, in stream order), so
+ * back-to-back calls on one stream are safe; calls that OVERLAP on one GPU (two streams, two host
+ * threads) race on it and give wrong sums on the corner diagonal. */
+#define STM_SGM_STATIC_MAX_FLOATS 524288
+int stm_sgm_static_f32(const float *cost, const float *left, float *out, int H, int W, int D,
+                       float penalty1, float penalty2, unsigned flags, void *stream);
+
 /* Measurement API (new; bench.py's per-pass roofline lines).  With timing enabled, every
  * stm_sgm_f32 / stm_sgm_wta_f32 call records CUDA events on its stream around each of the
  * passes (a pass = one direction's kernel plus its corner-diagonal replay, see SURVEY.md F5, or

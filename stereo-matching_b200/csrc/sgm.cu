@@ -846,4 +846,76 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
               "D %% 64 == 0, else <= 256)", D);
 }
 
+// ---- stm_sgm_static_f32: aggregation without any allocation by the caller or the library ------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The
+// per-direction schedule's only scratch -- the L vectors of the corner up-diagonal that the
+// reference re-runs W-H times (min(H, W) * Dpad floats) -- lives in this file-scope
+// device array instead of a caller-provided workspace.  2 MiB per GPU that loads the library, held
+// until exit.  Every call on a device shares it and it keeps the last call's contents: nothing in
+// it has to start at zero (the store pass writes every element the replay reads, in stream order),
+// but two calls that OVERLAP on one GPU (different streams / host threads) race on it.
+constexpr size_t kSgmStaticScratchFloats = STM_SGM_STATIC_MAX_FLOATS;  // 2 MiB (include/stm_abi.h)
+static __device__ __align__(256) float g_sgm_static_scratch[kSgmStaticScratchFloats];
+
+// In host code `g_sgm_static_scratch` is a host-side stand-in, not a device address: the address
+// is taken once per device, with that device current, and cached per ordinal.
+static int sgm_static_scratch(float **out) {
+  static std::mutex mu;
+  static float *ptr[kMaxDevices] = {nullptr};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    cudaGetLastError();
+    return fail(STM_ECUDA, "sgm_static: no usable CUDA device (libstm_b200 has no CPU fallback)");
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr[dev] == nullptr) {
+    void *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_sgm_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      cudaGetLastError();
+      return fail(STM_ECUDA, "Cuda call error cudaGetSymbolAddress(g_sgm_static_scratch): %s",
+                  cudaGetErrorString(e));
+    }
+    ptr[dev] = static_cast<float *>(p);
+  }
+  *out = ptr[dev];
+  return STM_OK;
+}
+
 }  // namespace stm
+
+extern "C" int stm_sgm_static_f32(const float *cost, const float *left, float *out, int H, int W, int D,
+                                  float penalty1, float penalty2, unsigned flags, void *stream) {
+  using namespace stm;
+  int rc = check_shape("sgm_static", H, W, D);
+  if (rc) return rc;
+  if (!cost || !left || !out) return fail(STM_EINVAL, "sgm_static: null pointer");
+  if (cost == out) return fail(STM_EINVAL, "sgm_static: output must not alias the cost volume");
+  if (flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE))
+    return fail(STM_EINVAL, "sgm_static: unknown flags 0x%x (STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE only)", flags);
+  if (D < 2) return fail(STM_EINVAL, "sgm_static: D must be >= 2");
+  if (H > 32767 || W > 32767) return fail(STM_EINVAL, "sgm_static: H and W must be <= 32767");
+  const LaneMap m = pick_lane_map(D);
+  const size_t need = (size_t)(H < W ? H : W) * m.NV * 32 * m.VW;
+  if (need > kSgmStaticScratchFloats)
+    return fail(STM_EINVAL, "sgm_static: min(H, W) * padded D = %zu floats exceeds the built-in scratch of %zu "
+                "floats (2 MiB); use stm_sgm_f32 with a workspace", need, kSgmStaticScratchFloats);
+  float *ws = nullptr;
+  if ((rc = sgm_static_scratch(&ws))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the eight direction passes one after the other, in the reference's order: exactly what
+  // stm_sgm_f32 runs with STM_SGM_SEQUENTIAL
+#define STM_SGM_ST(NV_, VW_)                                                                                  \
+  if (m.NV == NV_ && m.VW == VW_)                                                                             \
+    return H > W ? sgm_by_direction_portrait<NV_, VW_>(cost, left, out, H, W, D, penalty1, penalty2, flags,   \
+                                                       ws, st, nullptr)                                       \
+                 : sgm_by_direction<NV_, VW_>(cost, left, out, H, W, D, penalty1, penalty2, flags, ws, st,    \
+                                              nullptr);
+  STM_SGM_ST(1, 4) STM_SGM_ST(2, 4) STM_SGM_ST(3, 4) STM_SGM_ST(4, 4)
+  STM_SGM_ST(1, 2) STM_SGM_ST(3, 2) STM_SGM_ST(5, 2) STM_SGM_ST(7, 2)
+  STM_SGM_ST(1, 1) STM_SGM_ST(2, 1) STM_SGM_ST(3, 1) STM_SGM_ST(4, 1)
+  STM_SGM_ST(5, 1) STM_SGM_ST(6, 1) STM_SGM_ST(7, 1) STM_SGM_ST(8, 1)
+#undef STM_SGM_ST
+  return fail(STM_EUNSUPPORTED, "sgm_static: D=%d not supported", D);
+}
