@@ -221,8 +221,10 @@ static int run_dp(const float *cost, int8_t *path, float *row_final, int32_t *di
   const int blocks = (H + warps - 1) / warps;
   bool deep = false;
   if (NV * VW <= 4) {
-    static int resident = -1;  // per instantiation
-    if (resident < 0) {
+    static PerDeviceInt cache;  // per instantiation and device
+    const int dev = device_slot();
+    int resident = 0;
+    if (!cache.get(dev, &resident)) {
       int nb = 0;
       if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, dp_row_kernel<NV, VW, true>, warps * 32,
                                                         0) != cudaSuccess) {
@@ -230,6 +232,7 @@ static int run_dp(const float *cost, int8_t *path, float *row_final, int32_t *di
         nb = 0;
       }
       resident = nb * warps * num_sms();
+      cache.set(dev, resident);
     }
     deep = H <= resident;
   }
@@ -239,6 +242,8 @@ static int run_dp(const float *cost, int8_t *path, float *row_final, int32_t *di
     dp_row_kernel<NV, VW, false><<<blocks, warps * 32, 0, stream>>>(cost, path, row_final, disp, H, W, D);
   return check_launch("dp_row_kernel");
 }
+
+int launch_dp_bulk(const float *, int8_t *, float *, int32_t *, int, int, int, cudaStream_t);  // dp_bulk.cu
 
 int launch_dp(const float *cost, int8_t *path, float *row_final, int32_t *disp, int H, int W,
               int D, unsigned flags, cudaStream_t stream) {
@@ -254,6 +259,10 @@ int launch_dp(const float *cost, int8_t *path, float *row_final, int32_t *disp, 
     if (rc) return rc;
     dp_backtrack_kernel<<<(H + 63) / 64, 64, 0, stream>>>(path, row_final, disp, H, W, D);
     return check_launch("dp_backtrack_kernel");
+  }
+  {  // D % 64 == 0: cost tiles through the bulk-copy engine, prefetched backtrack (dp_bulk.cu)
+    const int rc = launch_dp_bulk(cost, path, row_final, disp, H, W, D, stream);
+    if (rc != 1) return rc;
   }
   const LaneMap m = pick_lane_map(D);
 #define STM_DP_CASE(NV_, VW_) \
