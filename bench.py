@@ -337,7 +337,16 @@ def run_b200_arm(args):
 
     passes = []
     fused = len(pass_ms) == 4  # horizontal passes + two fused vertical sweeps (sgm_vsweep.cu)
+    overlapped = len(pass_ms) == 2  # STM_SGM_OVERLAP: (-> <- on a helper stream || down sweep), up sweep
     for (k, d), t in sorted(pass_ms.items()):
+        if overlapped:
+            # phase 0: -> writes S (8 B), <- read-modify-writes S (12 B), down sweep reads C and
+            # writes T (8 B); phase 1: up sweep reads C, S, T and writes S (16 B)
+            b = H * W * D * 4 * (7 if k == 0 else 4) + H * W * 4 * (3 if k == 0 else 1)
+            label = "0,1 || 2+4+6" if k == 0 else "3+5+7 (+T)"
+            passes.append({"dir": label, "ms": round(t, 4), "bytes": b, "GBs": round(b / (t * 1e-3) / 1e9, 1),
+                           "frac_of_peak": round(b / (t * 1e-3) / 1e9 / peak, 3)})
+            continue
         b = sgm_pass_bytes(d, k == 0, H, W, D, fused_sweep=fused and k >= 2)
         label = {2: "2+4+6", 3: "3+5+7"}[d] if fused and k >= 2 else str(d)
         passes.append({"dir": label, "ms": round(t, 4), "bytes": b, "GBs": round(b / (t * 1e-3) / 1e9, 1),
@@ -450,7 +459,7 @@ def run_b200_arm(args):
         "ms_per_frame": ms / args.steps / F, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "1920x1080 D=128 SSD(k=7)+SGM(P1=.1,P2=.2, reference path set; 2 horizontal "
-                               "passes + 2 fused vertical sweeps)+WTA, "
+                               "passes next to the down sweep, then the up sweep)+WTA, "
                                "random-dot stereograms", "frames_per_gpu_per_step": F,
                    "frames_in_flight": 2,
                    "sharding": f"frame-sharded x{world}, no collective",

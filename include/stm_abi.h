@@ -63,6 +63,15 @@ extern "C" {
                                   concurrently into per-direction buffers of the workspace and
                                   add them in the reference's order -- bit-identical results. */
 
+#define STM_SGM_OVERLAP 32u /* with STM_SGM_FUSED_SWEEPS: the two horizontal passes run on a library-owned
+                               helper stream NEXT TO the down sweep, which writes a volume T of its own
+                               in the workspace; the up sweep adds out + T.  Same passes and bytes, less
+                               time (the sweeps are latency-bound and leave half the bandwidth idle).
+                               Needs stm_sgm_workspace_bytes_flags(H, W, D, flags) bytes of workspace
+                               (one more volume); padded D <= 128 (at D = 192 it measured slower).  Falls back to the plain fused schedule
+                               when the shape or the workspace does not allow it.  Sum associated
+                               ((L0 + L1) + (L2+L4+L6)) + L3 + L5 + L7: within 1e-4, not bit-identical. */
+
 /* flags of stm_dp_f32 */
 #define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68);
                                requires D <= H <= W and a zeroed path volume */
@@ -97,6 +106,10 @@ int stm_birchfield_f32(const float *left, const float *right, float *cost, int H
  * shapes run the eight directions concurrently on library-owned streams that are forked from and
  * joined to `stream`; see STM_SGM_SEQUENTIAL).  The query is a pure function of the shape. */
 size_t stm_sgm_workspace_bytes(int H, int W, int D);
+/* The same query for calls that pass `flags` (today only STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP asks
+ * for more than stm_sgm_workspace_bytes).  New; the reference allocates its scratch itself
+ * (thrust::device_vector per call, src/semiglobal_gpu.cu:126). */
+size_t stm_sgm_workspace_bytes_flags(int H, int W, int D, unsigned flags);
 int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, int D,
                 float penalty1, float penalty2, unsigned flags, void *workspace,
                 size_t workspace_bytes, void *stream);

@@ -63,8 +63,10 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         list(ex.map(compile_one, jobs))
     objs = [OBJ / (s.stem + ".o") for s in sources()]
     if force or jobs or _stale(OUT, objs):
+        # --no-undefined: a launcher whose signature drifted from its declaration in another
+        # translation unit must fail HERE, not when the library is loaded on the GPU box
         cmd = [nvcc, "-shared", "-o", str(OUT), *map(str, objs),
-               "-gencode", "arch=compute_100a,code=sm_100a"]
+               "-gencode", "arch=compute_100a,code=sm_100a", "-Xlinker", "--no-undefined"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stderr}")

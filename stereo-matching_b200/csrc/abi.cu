@@ -17,6 +17,7 @@ int launch_wta(const float *, int32_t *, int, int, int, cudaStream_t);
 int launch_ssd(const float *, const float *, float *, int, int, int, int, cudaStream_t);
 int launch_birchfield(const float *, const float *, float *, int, int, int, cudaStream_t);
 size_t sgm_workspace_bytes(int, int, int);
+size_t sgm_workspace_bytes_flags(int, int, int, unsigned);
 int sgm_pass_timing(bool);
 int sgm_last_pass_ms(float *, int *, int);
 int launch_sgm(const float *, const float *, float *, int, int, int, float, float, unsigned, void *,
@@ -106,6 +107,11 @@ size_t stm_sgm_workspace_bytes(int H, int W, int D) {
   return sgm_workspace_bytes(H, W, D);
 }
 
+size_t stm_sgm_workspace_bytes_flags(int H, int W, int D, unsigned flags) {
+  if (H <= 0 || W <= 0 || D <= 0) return 0;
+  return sgm_workspace_bytes_flags(H, W, D, flags);
+}
+
 int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, int D,
                 float penalty1, float penalty2, unsigned flags, void *workspace,
                 size_t workspace_bytes, void *stream) {
@@ -113,7 +119,7 @@ int stm_sgm_f32(const float *cost, const float *left, float *out, int H, int W, 
   if (rc) return rc;
   STM_REQUIRE(cost && left && out, "sgm: null pointer");
   STM_REQUIRE(cost != out, "sgm: output must not alias the cost volume");
-  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_FUSED_SWEEPS | STM_SGM_SEQUENTIAL)) == 0, "sgm: unknown flags 0x%x",
+  STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_FUSED_SWEEPS | STM_SGM_SEQUENTIAL | STM_SGM_OVERLAP)) == 0, "sgm: unknown flags 0x%x",
               flags);
   if ((rc = require_device())) return rc;
   return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace,
@@ -128,7 +134,7 @@ int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *d
   STM_REQUIRE(cost && left && out && disparity, "sgm_wta: null pointer");
   STM_REQUIRE(cost != out, "sgm_wta: output must not alias the cost volume");
   STM_REQUIRE((flags & ~(STM_SGM_MIN_ALL_D | STM_SGM_OVERWRITE | STM_SGM_DISPARITY_ONLY | STM_SGM_SEQUENTIAL |
-                         STM_SGM_FUSED_SWEEPS)) == 0,
+                         STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP)) == 0,
               "sgm_wta: unknown flags 0x%x", flags);
   if ((rc = require_device())) return rc;
   return launch_sgm(cost, left, out, H, W, D, penalty1, penalty2, flags, workspace, workspace_bytes,
@@ -191,7 +197,7 @@ int stm_pipeline_host_f32(const float *left, const float *right, int32_t *dispar
   if (rc) return rc;
   float *vol = dc;
   if (use_sgm) {
-    const size_t wsb = sgm_workspace_bytes(H, W, D);
+    const size_t wsb = sgm_workspace_bytes_flags(H, W, D, sgm_flags);
     if ((rc = s.ensure(kS, N * 4)) || (rc = s.ensure(kWs, wsb ? wsb : 16))) return rc;
     const bool fuse_wta = reducer == 0;
     rc = launch_sgm(dc, dl, (float *)s.ptr[kS], H, W, D, penalty1, penalty2,

@@ -14,11 +14,12 @@
 //   * a cost row is contiguous in [H,W,D], so lane 0 streams it in tiles of a few columns with
 //     cp.async.bulk (global -> shared, completion on the stage's mbarrier), four tiles ahead; the
 //     warp reads the vectors back from shared memory.  No prefetch registers, no scoreboards;
-//   * the backtrack loads the WHOLE path vector of a column (D bytes: VW bytes per lane and lane
-//     vector, the layout the forward pass wrote).  Those loads do not depend on e, so three blocks
-//     of 16 columns are kept in flight while a block is resolved with one shuffle per column.
+//   * the backtrack streams the row's path bytes back through the same stages (tiles of up to 32
+//     columns, whole vectors: those copies do not depend on e).  e is warp-uniform, so every lane
+//     reads the byte tile[col][e] itself: no shuffle, two instructions on the chain per column.
 // Each warp owns its stages and barriers: no CTA-wide barrier, a warp past the last row exits.
 #include <cstdlib>
+#include <type_traits>
 
 #include "lanevec.cuh"
 #include "sgm_paths.cuh"
@@ -28,7 +29,6 @@ namespace dpb {
 
 constexpr int kWarps = 4;
 constexpr int kStages = 4;
-constexpr int kBlockCols = 16;  // backtrack: columns resolved per block
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, int count) {
@@ -61,8 +61,6 @@ struct Cfg {
   static constexpr int kTileFloats = kTile * kD;
   static constexpr size_t kWarpBytes = (size_t)kStages * kTileFloats * sizeof(float);
   static constexpr size_t kSmemBytes = kWarps * kWarpBytes + kWarps * kStages * sizeof(uint64_t);
-  // backtrack blocks in flight, bounded by registers (kBlockCols * NV words per block)
-  static constexpr int kBlocks = NV == 1 ? 3 : (NV == 2 ? 2 : 1);
 };
 
 }  // namespace dpb
@@ -188,58 +186,60 @@ dp_row_bulk_kernel(const float *__restrict__ cost, int8_t *__restrict__ path, fl
   int e = idx == 0x7fffffff ? 0 : idx;
 
   // ---- backtrack: e(col) = clamp(e(col+1) + path[row][col][e(col+1)], 0, D-1), col = W-2 .. 0.
-  // Lane l loads, for each of the next kBlockCols columns, the VW path bytes it wrote itself in the
-  // forward pass for each lane vector k (d = k*32*VW + l*VW ..): the whole column vector sits in
-  // the warp, whatever e turns out to be.  kBlocks blocks are in flight; a step is: pick vector
-  // k = e / (32 VW) (warp-uniform), shuffle from lane (e % (32 VW)) / VW, take byte e % VW.
-  // The bytes were written by other lanes of this warp: __syncwarp orders them, .cg reads them at L2.
+  // The row's path bytes are contiguous as well, so they come back the way the costs came in: tiles
+  // of BTC columns (BTC * D bytes, at most one stage) by cp.async.bulk into the SAME stages, kStages
+  // tiles ahead.  With a column's whole vector in shared memory no shuffle is needed: e is
+  // warp-uniform, every lane reads the one byte tile[col][e] (a broadcast) and keeps the e of the
+  // column whose index equals its lane; a tile ends with one coalesced store of BTC disparities.
+  // The chain per column is LDS.S8 + add-and-clamp.
+  // The bytes were written by this warp's generic-proxy stores and are read by the async proxy:
+  // __syncwarp orders the lanes' stores, fence.proxy.async orders them before the bulk copies.
   __syncwarp();
-  constexpr int BC = kBlockCols, NB = C::kBlocks;
+  asm volatile("fence.proxy.async;" ::: "memory");
+  constexpr int BTC = (int)((C::kTileFloats * sizeof(float)) / D) < 32 ? (int)((C::kTileFloats * sizeof(float)) / D) : 32;
+  static_assert(BTC >= 1 && BTC <= 32, "backtrack tile");
   int32_t *drow = disp + row_off;
-  const unsigned char *pr = reinterpret_cast<const unsigned char *>(prow_w) + lane * VW;
+  const signed char *prow_r = reinterpret_cast<const signed char *>(prow_w);
   if (lane == 0) drow[W - 1] = e;
-  const int nblk = (W - 1 + BC - 1) / BC;  // block b: columns W-2-b*BC-j, j = 0..BC-1
-  unsigned w[NB][BC][NV];
-  auto load_block = [&](unsigned (&dst)[BC][NV], int b) {
-#pragma unroll
-    for (int j = 0; j < BC; ++j) {
-      int c = W - 2 - b * BC - j;
-      c = c < 0 ? 0 : c;  // clamped: always a valid address, the value is not used
-      const unsigned char *q = pr + (size_t)c * D;
-#pragma unroll
-      for (int k = 0; k < NV; ++k) {
-        if constexpr (VW == 4) dst[j][k] = __ldcg(reinterpret_cast<const unsigned *>(q + k * 32 * VW));
-        else dst[j][k] = __ldcg(reinterpret_cast<const unsigned short *>(q + k * 32 * VW));
-      }
-    }
+  const int nbt = (W - 1 + BTC - 1) / BTC;  // tile b: columns hi = W-2-b*BTC down to lo = max(hi-BTC+1, 0)
+  auto bt_issue = [&](int b) {              // lane 0; sequence number ntiles + b continues the stage/phase order
+    const int g = ntiles + b, st = g % kStages;
+    const int hi = W - 2 - b * BTC, lo = hi - BTC + 1 < 0 ? 0 : hi - BTC + 1;
+    const uint32_t bytes = (uint32_t)(hi - lo + 1) * D;
+    const uint32_t bar = smem_u32(bars + st);
+    mbar_expect_tx(bar, bytes);
+    bulk_g2s(smem_u32(stages + st * TF), prow_r + (size_t)lo * D, bytes, bar);
   };
-#pragma unroll
-  for (int s = 0; s < NB; ++s) load_block(w[s], s < nblk ? s : 0);
+  if (lane == 0)
+    for (int b = 0; b < kStages && b < nbt; ++b) bt_issue(b);
 
-  for (int b0 = 0; b0 < nblk; b0 += NB) {
+  auto bt_resolve = [&](auto full_tag, const signed char *tile, int ncols_tile, int hi) {
+    constexpr bool FULL_TILE = decltype(full_tag)::value;  // all BTC columns exist: no test per step
+    // column hi - j sits at tile row (ncols_tile - 1 - j)
+    const signed char *top = tile + (size_t)(ncols_tile - 1) * D;
+    int mine = 0;
 #pragma unroll
-    for (int s = 0; s < NB; ++s) {
-      const int b = b0 + s;
-      if (b < nblk) {  // warp-uniform
-        const int c_first = W - 2 - b * BC;
-        int mine = 0;
-#pragma unroll
-        for (int j = 0; j < BC; ++j) {
-          const int k = e / (32 * VW), rem = e - k * (32 * VW);
-          unsigned word = w[s][j][0];
-#pragma unroll
-          for (int kk = 1; kk < NV; ++kk) word = (k == kk) ? w[s][j][kk] : word;
-          const unsigned got = __shfl_sync(FULL, word, rem / VW);
-          const int v = (int)(signed char)((got >> (8 * (rem % VW))) & 0xffu);
-          int en = e + v;
-          en = en < 0 ? 0 : (en > D - 1 ? D - 1 : en);
-          if (c_first - j >= 0) e = en;
-          if (lane == j) mine = e;
-        }
-        if (lane < BC && c_first - lane >= 0) drow[c_first - lane] = mine;
-        load_block(w[s], b + NB < nblk ? b + NB : 0);
+    for (int j = 0; j < BTC; ++j) {
+      if (FULL_TILE || j < ncols_tile) {
+        const int v = top[e - j * D];
+        int en = e + v;
+        en = en < 0 ? 0 : (en > D - 1 ? D - 1 : en);
+        e = en;
       }
+      if (lane == j) mine = e;
     }
+    if (lane < ncols_tile) drow[hi - lane] = mine;
+  };
+
+  for (int b = 0; b < nbt; ++b) {
+    const int g = ntiles + b, st = g % kStages;
+    mbar_wait(smem_u32(bars + st), (uint32_t)(g / kStages) & 1u);
+    const int hi = W - 2 - b * BTC, lo = hi - BTC + 1 < 0 ? 0 : hi - BTC + 1;
+    const signed char *tile = reinterpret_cast<const signed char *>(stages + st * TF);
+    if (hi - lo + 1 == BTC) bt_resolve(std::true_type{}, tile, BTC, hi);
+    else bt_resolve(std::false_type{}, tile, hi - lo + 1, hi);
+    __syncwarp();  // every lane has read the tile: its stage can be refilled
+    if (lane == 0 && b + kStages < nbt) bt_issue(b + kStages);
   }
 }
 
@@ -267,7 +267,7 @@ static int run_dp_bulk(const float *cost, int8_t *path, float *row_final, int32_
 int launch_dp_bulk(const float *cost, int8_t *path, float *row_final, int32_t *disp, int H, int W, int D,
                    cudaStream_t stream) {
   if (D % 64 != 0 || W < 2) return 1;
-  if ((reinterpret_cast<uintptr_t>(cost) & 15) || (reinterpret_cast<uintptr_t>(path) & 3) ||
+  if ((reinterpret_cast<uintptr_t>(cost) & 15) || (reinterpret_cast<uintptr_t>(path) & 15) ||
       (reinterpret_cast<uintptr_t>(row_final) & 15))
     return 1;
   {

@@ -578,10 +578,11 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
 
 // sgm_vsweep.cu
 size_t sgm_vsweep_workspace_bytes(int H, int W, int D);
-bool sgm_vsweep_can_run(int H, int W, int D);
+bool sgm_vsweep_can_run(int H, int W, int D, bool three_streams);
 int launch_sgm_vsweep_prepare(const float *, int, int, int, float, float, void *, cudaStream_t);
-int launch_sgm_vsweep(const float *, const float *, float *, int32_t *, int, int, int, float, float,
-                      int, int, bool, void *, size_t, cudaStream_t);
+int launch_sgm_vsweep(const float *cost, const float *image, float *out, const float *extra, int32_t *disp,
+                      int H, int W, int D, float p1, float p2, int min_limit, int up, bool store_vol,
+                      int volume_streams, void *workspace, size_t workspace_bytes, cudaStream_t stream);
 
 // STM_SGM_FUSED_SWEEPS: the two horizontal directions as passes of their own, then the six
 // directions with a vertical component as two fused sweeps (sgm_vsweep.cu): four passes over
@@ -592,7 +593,7 @@ static int sgm_fused(const float *cost, const float *image, float *out, int H, i
                      float p1, float p2, unsigned flags, void *ws, size_t ws_bytes,
                      cudaStream_t stream, int32_t *disp) {
   const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
-  if (ws == nullptr || ws_bytes < sgm_vsweep_workspace_bytes(H, W, D) || !sgm_vsweep_can_run(H, W, D))
+  if (ws == nullptr || ws_bytes < sgm_vsweep_workspace_bytes(H, W, D) || !sgm_vsweep_can_run(H, W, D, false))
     return 1;
   if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) |
        reinterpret_cast<uintptr_t>(ws)) & 15)
@@ -607,13 +608,13 @@ static int sgm_fused(const float *cost, const float *image, float *out, int H, i
   }
   pass_mark(2, 2, stream);
   if ((rc = launch_sgm_vsweep_prepare(image, H, W, D, p1, p2, ws, stream))) return rc;
-  rc = launch_sgm_vsweep(cost, image, out, nullptr, H, W, D, p1, p2, min_limit, 0, true, ws,
+  rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 2, ws,
                          ws_bytes, stream);
   if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
   if (rc) return rc;
   pass_mark(3, 3, stream);
-  rc = launch_sgm_vsweep(cost, image, out, disp, H, W, D, p1, p2, min_limit, 1,
-                         !(disp && (flags & STM_SGM_DISPARITY_ONLY)), ws, ws_bytes, stream);
+  rc = launch_sgm_vsweep(cost, image, out, nullptr, disp, H, W, D, p1, p2, min_limit, 1,
+                         !(disp && (flags & STM_SGM_DISPARITY_ONLY)), 2, ws, ws_bytes, stream);
   if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
   if (rc) return rc;
   pass_mark(4, -1, stream);
@@ -646,6 +647,16 @@ size_t sgm_workspace_bytes(int H, int W, int D) {
   const size_t base = sgm_base_workspace_bytes(H, W, D);
   if (!sgm_concurrent_eligible(H, W, D)) return base;
   return align256(base) + (size_t)8 * H * W * D * sizeof(float);
+}
+static bool sgm_overlap_shape(int H, int W, int D);
+// with STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP: one more volume after the base workspace
+size_t sgm_workspace_bytes_flags(int H, int W, int D, unsigned flags) {
+  const size_t plain = sgm_workspace_bytes(H, W, D);
+  if ((flags & (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP)) != (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP) ||
+      !sgm_overlap_shape(H, W, D))
+    return plain;
+  const size_t need = align256(sgm_base_workspace_bytes(H, W, D)) + (size_t)H * W * D * sizeof(float);
+  return need > plain ? need : plain;
 }
 
 // out = [out +] b0 + b1 + ... + b7, one fp32 addition at a time in the reference's order; the
@@ -734,6 +745,86 @@ static int aux_streams(AuxStreams **out) {
   return STM_OK;
 }
 
+// STM_SGM_OVERLAP (with STM_SGM_FUSED_SWEEPS): the same four passes, but the horizontal passes run
+// NEXT TO the down sweep instead of before it.  In the plain fused schedule everything chains
+// through `out` (-> writes it, <- and both sweeps read-modify-write it), so 0.98 ms of
+// bandwidth-bound horizontal passes (0.82-0.85 of the copy rate) sit in front of 1.44 ms of sweeps
+// that are bound by hand-off latency and issue slots and use about half the bandwidth.  With one
+// more volume T in the workspace nothing has to chain:
+//     stream:       penalties, down sweep  T   = L2 + L4 + L6        (reads C, writes T: 8 B/pix-disp)
+//     helper:       ->  out  = [out +] L0 ;  <-  out += L1           (8 + 12 B, concurrently)
+//     stream:       up sweep   out = (out + T) + L3 + L5 + L7, argmin  (reads C, out, T)
+// Same bytes as before (40-44 B/pix-disp); the sweep CTA (one per SM, 94 KB of shared memory in
+// its overwrite form) leaves room for a 96 KB CTA of sgm_row_kernel on every SM.  The sum is
+// associated ((L0 + L1) + (L2+L4+L6)) + L3 + L5 + L7: within the 1e-4 bar like the plain fused
+// schedule, not bit-identical to it.  Developer knob STM_DEBUG_SGM_OVERLAP=x selects the other
+// variant that was measured (-> and <- concurrently with each other, <- into T, then both sweeps).
+static size_t sgm_base_workspace_bytes(int H, int W, int D);
+static size_t align256(size_t x);
+static size_t sgm_overlap_offset(int H, int W, int D) { return align256(sgm_base_workspace_bytes(H, W, D)); }
+static bool sgm_overlap_shape(int H, int W, int D) {  // pure function of the shape (workspace query)
+  if (H < 2 || W < 2 || sgm_vsweep_workspace_bytes(H, W, D) == 0) return false;
+  const LaneMap m = pick_lane_map(D);
+  // measured at 1080p: D=128 2.44 -> 2.23 ms; D=192 3.36 -> 3.65 ms (the three-stream up sweep has to
+  // give up a row of prefetch to fit in shared memory), so only up to 128 padded disparities
+  return m.NV * 32 * m.VW <= 128;
+}
+
+template <int NV, int VW>
+static int sgm_fused_overlap(const float *cost, const float *image, float *out, int H, int W, int D,
+                             float p1, float p2, unsigned flags, void *ws, size_t ws_bytes,
+                             cudaStream_t stream, int32_t *disp) {
+  const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
+  const size_t N = (size_t)H * W * D, off = sgm_overlap_offset(H, W, D);
+  if (!sgm_overlap_shape(H, W, D) || ws == nullptr || ws_bytes < off + N * sizeof(float) ||
+      !sgm_vsweep_can_run(H, W, D, true))
+    return 1;
+  if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(ws)) & 15)
+    return 1;
+  float *T = reinterpret_cast<float *>(static_cast<char *>(ws) + off);
+  static const char *knob = getenv("STM_DEBUG_SGM_OVERLAP");
+  const bool variant_x = knob && (knob[0] == 'x' || knob[0] == 'X');
+  AuxStreams *aux = nullptr;
+  int rc = aux_streams(&aux);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> enqueue_lock(aux->mu);  // fork ... join is one critical section
+  cudaStream_t helper = aux->stream[0];
+  const unsigned mode0 = (flags & STM_SGM_OVERWRITE) ? 0u : kSgmAccumulate;
+  const bool store_up = !(disp && (flags & STM_SGM_DISPARITY_ONLY));
+  pass_mark(0, 8, stream);
+  if (cudaEventRecord(aux->fork, stream) != cudaSuccess || cudaStreamWaitEvent(helper, aux->fork, 0) != cudaSuccess)
+    return fail(STM_ECUDA, "sgm: stream fork failed");
+  if ((rc = launch_sgm_vsweep_prepare(image, H, W, D, p1, p2, ws, stream))) return rc;
+  if (!variant_x) {
+    // the cooperative sweep first: it needs a slot on every SM; the row CTAs then fill what is left
+    rc = launch_sgm_vsweep(cost, image, T, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 1, ws, ws_bytes, stream);
+    if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
+    if (rc) return rc;
+    if ((rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 0, 0, H, min_limit, mode0, nullptr, -1, helper)))
+      return rc;
+    if ((rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 1, 0, H, min_limit, kSgmAccumulate, nullptr, -1, helper)))
+      return rc;
+    if (cudaEventRecord(aux->join[0], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[0], 0) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: stream join failed");
+  } else {
+    if ((rc = run_direction<NV, VW>(cost, image, T, H, W, D, p1, p2, 1, 0, H, min_limit, 0u, nullptr, -1, helper)))
+      return rc;
+    if ((rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 0, 0, H, min_limit, mode0, nullptr, -1, stream)))
+      return rc;
+    rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 2, ws, ws_bytes, stream);
+    if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
+    if (rc) return rc;
+    if (cudaEventRecord(aux->join[0], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[0], 0) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: stream join failed");
+  }
+  pass_mark(1, 3, stream);
+  rc = launch_sgm_vsweep(cost, image, out, T, disp, H, W, D, p1, p2, min_limit, 1, store_up, 3, ws, ws_bytes, stream);
+  if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
+  if (rc) return rc;
+  pass_mark(2, -1, stream);
+  return STM_OK;
+}
+
 int launch_wta(const float *, int32_t *, int, int, int, cudaStream_t);  // wta.cu
 
 template <int NV, int VW>
@@ -806,6 +897,14 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   if (flags & STM_SGM_FUSED_SWEEPS) {
     // opt-in: horizontal passes + two fused vertical sweeps (sgm_vsweep.cu); 1 = not handled
     int rc = 1;
+    if (flags & STM_SGM_OVERLAP) {
+#define STM_SGM_FO(NV_, VW_)        \
+  if (m.NV == NV_ && m.VW == VW_)   \
+    rc = sgm_fused_overlap<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, workspace, workspace_bytes, stream, disp);
+      STM_SGM_FO(1, 4) STM_SGM_FO(1, 2) STM_SGM_FO(3, 2) STM_SGM_FO(1, 1)
+#undef STM_SGM_FO
+      if (rc != 1) return rc;
+    }
 #define STM_SGM_FS(NV_, VW_)        \
   if (m.NV == NV_ && m.VW == VW_)   \
     rc = sgm_fused<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, workspace, workspace_bytes, stream, disp);

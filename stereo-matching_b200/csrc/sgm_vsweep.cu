@@ -94,22 +94,28 @@ constexpr bool kDebug = true;   // STM_DEBUG_VSWEEP knobs, statistics and trace 
 constexpr bool kDebug = false;
 #endif
 
-template <int DPAD>
+// NS = volume vectors prefetched per pixel: 1 = cost only (the sweep OVERWRITES `out` with its three
+// directions: no sum is read), 2 = cost + sum (read-modify-write of `out`), 3 = cost + sum + one more
+// volume `extra` that is added too (the other sweep's result, when the two sweeps did not chain
+// through `out`; see sgm.cu, STM_SGM_OVERLAP).
+template <int DPAD, int NS = 2>
 struct Cfg {
-  static constexpr int PF = DPAD <= 192 ? kPfSmall : 4;  // prefetch ring entries per slot (PF-1 rows ahead)
+  static constexpr int PF = (DPAD <= 128 || (DPAD <= 192 && NS <= 2)) ? kPfSmall : 4;  // prefetch ring entries per slot
   static constexpr int kBarOff = 0;                                    // (full, empty)[kCols + 2][kR]
   static constexpr int kCreditOff = 1008;                              // unsigned: rows the previous CTA has imported
   static constexpr int kRingBOff = 1024;                               // [kCols+1][kR][DPAD]
   static constexpr int kRingCOff = kRingBOff + (kCols + 1) * kR * DPAD * 4;  // [kCols+2][kR][DPAD]
-  static constexpr int kPfOff = kRingCOff + (kCols + 2) * kR * DPAD * 4;     // [kCols][PF][2][DPAD]
-  static constexpr int kPfiOff = kPfOff + kCols * PF * 2 * DPAD * 4;         // [kCols][PF] float4 penalties
+  static constexpr int kPfOff = kRingCOff + (kCols + 2) * kR * DPAD * 4;     // [kCols][PF][NS][DPAD]
+  static constexpr int kPfiOff = kPfOff + kCols * PF * NS * DPAD * 4;        // [kCols][PF] float4 penalties
   static constexpr int kBytes = kPfiOff + kCols * PF * 16;
+  static constexpr bool kFits = kBytes <= 227 * 1024;
 };
 
 struct Params {
   const float *cost;
   const float4 *pen;          // [H][W] adaptive penalties (A, B, C, -) of this sweep, see sgm_vsweep_penalties
   float *out;
+  const float *extra;         // NS == 3: a second sum volume that is added (read only)
   int32_t *disp;
   unsigned long long *xring;  // [G][kRX][3][DPAD] (value, tag) words
   unsigned *xcons;            // [G][kFlagStride] rows imported so far by CTA c (one 128-byte line each)
@@ -448,10 +454,10 @@ __device__ __forceinline__ void add_weighted(LaneVec<NV, VW> &o, const LaneVec<N
   }
 }
 
-template <int NV, int VW, bool UP, bool WTA>
+template <int NV, int VW, bool UP, bool WTA, int NS>
 __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int base, int j, int lane) {
   constexpr int DPAD = NV * 32 * VW;
-  using C = Cfg<DPAD>;
+  using C = Cfg<DPAD, NS>;
   constexpr int PF = C::PF;
   const int H = P.H, W = P.W, D = P.D;
   constexpr bool up = UP;
@@ -462,7 +468,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   const unsigned bars = (unsigned)__cvta_generic_to_shared(smem + C::kBarOff);
   float *ringB = reinterpret_cast<float *>(smem + C::kRingBOff) + (size_t)j * kR * DPAD + lane_off;
   float *ringC = reinterpret_cast<float *>(smem + C::kRingCOff) + (size_t)j * kR * DPAD + lane_off;
-  float *pf = reinterpret_cast<float *>(smem + C::kPfOff) + (size_t)j * PF * 2 * DPAD + lane_off;
+  float *pf = reinterpret_cast<float *>(smem + C::kPfOff) + (size_t)j * PF * NS * DPAD + lane_off;
   float4 *pfi = reinterpret_cast<float4 *>(smem + C::kPfiOff) + j * PF;  // lane 0 copies, all read
 
   const long long rowstep = up ? -(long long)W : (long long)W;
@@ -470,6 +476,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   // fetch side: row pointers (lane offset included) + column
   const float *crow = P.cost + (long long)y * W * D + lane_off;
   const float *srow = P.out + (long long)y * W * D + lane_off;
+  const float *xrow = (NS == 3 ? P.extra : P.out) + (long long)y * W * D + lane_off;
   const float4 *prow = P.pen + (long long)y * W;
   const long long rowstep_d = rowstep * D;
   int fx = x, ft = 0;
@@ -477,21 +484,22 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   // row ft: cost, sum and penalties into ring entry `e`; always exactly one commit group.
   // Past the last row the last row is fetched again (never used).
   auto issue = [&](int e) {
-    const float *cs = crow + fx * D, *ss = srow + fx * D;
-    float *dc = pf + e * 2 * DPAD;
+    const float *cs = crow + fx * D, *ss = srow + fx * D, *xs = xrow + fx * D;
+    float *dc = pf + e * NS * DPAD;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int off = k * 32 * VW;
       if ((VW > 1 || off + lane < D) && !(kDebug && (P.dbg & 32))) {
         cp_async<VW * 4>(dc + off, cs + off);
-        cp_async<VW * 4>(dc + DPAD + off, ss + off);
+        if constexpr (NS >= 2) cp_async<VW * 4>(dc + DPAD + off, ss + off);
+        if constexpr (NS == 3) cp_async<VW * 4>(dc + 2 * DPAD + off, xs + off);
       }
     }
     if (lane == 0) cp_async<16>(reinterpret_cast<float *>(pfi + e), reinterpret_cast<const float *>(prow + fx));
     cp_async_commit();
     if (ft + 1 < H) {
       ++ft;
-      prow += rowstep; crow += rowstep_d; srow += rowstep_d;
+      prow += rowstep; crow += rowstep_d; srow += rowstep_d; xrow += rowstep_d;
       fx = fx + 1 == W ? 0 : fx + 1;
     }
   };
@@ -524,8 +532,25 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       if (stats) st_mem += clock64() - c0;
     }
     LaneVec<NV, VW> c, o;
-    lv_lds<NV, VW>(c, pf + e * 2 * DPAD, 0);
-    lv_lds<NV, VW>(o, pf + e * 2 * DPAD + DPAD, 0);
+    lv_lds<NV, VW>(c, pf + e * NS * DPAD, 0);
+    if constexpr (NS >= 2) {
+      lv_lds<NV, VW>(o, pf + e * NS * DPAD + DPAD, 0);
+    } else {
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int q = 0; q < VW; ++q) o.v[k][q] = 0.f;  // this sweep starts the sum (0 + L is exact)
+    }
+    if constexpr (NS == 3) {
+      LaneVec<NV, VW> x2;
+      lv_lds<NV, VW>(x2, pf + e * NS * DPAD + 2 * DPAD, 0);
+      if constexpr (VW == 1) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+          if (k * 32 + lane >= D) x2.v[k][0] = 0.f;
+      }
+      add_weighted<NV, VW>(o, x2, 1);
+    }
     if constexpr (VW == 1) {
 #pragma unroll
       for (int k = 0; k < NV; ++k)
@@ -630,10 +655,10 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   }
 }
 
-template <int NV, int VW, bool UP, bool WTA>
+template <int NV, int VW, bool UP, bool WTA, int NS>
 __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P) {
   extern __shared__ __align__(128) unsigned char smem[];
-  using C = Cfg<NV * 32 * VW>;
+  using C = Cfg<NV * 32 * VW, NS>;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int c = blockIdx.x;
   const int ncols = P.q + (c < P.r ? 1 : 0);
@@ -649,7 +674,7 @@ __global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P)
   __syncthreads();
   if (wid == kCols) importer_warp<NV, VW>(smem, P, ncols, lane);
   else if (wid == kCols + 1) exporter_warp<NV, VW>(smem, P, lane);
-  else if (wid < ncols) column_warp<NV, VW, UP, WTA>(smem, P, ncols, base, wid, lane);
+  else if (wid < ncols) column_warp<NV, VW, UP, WTA, NS>(smem, P, ncols, base, wid, lane);
 }
 
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
@@ -683,34 +708,52 @@ static size_t flags_and_rings_bytes(size_t dpad) {
          align256((size_t)kMaxCtas * kRX * 3 * dpad * sizeof(unsigned long long));
 }
 
-// CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.
+// The six variants of one lane map: (up?, argmin?, volume streams).  nullptr = does not fit in
+// shared memory for this lane map (three streams at D = 256).
+template <int NV, int VW, bool UP, bool WTA, int NS>
+static const void *variant(size_t *smem_bytes) {
+  using C = Cfg<NV * 32 * VW, NS>;
+  if constexpr (C::kFits) {
+    *smem_bytes = (size_t)C::kBytes;
+    return (const void *)sgm_vsweep_kernel<NV, VW, UP, WTA, NS>;
+  } else {
+    *smem_bytes = 0;
+    return nullptr;
+  }
+}
 template <int NV, int VW>
-static const void *sweep_kernel(bool up, bool wta) {
-  return !up ? (const void *)sgm_vsweep_kernel<NV, VW, false, false>
-             : (wta ? (const void *)sgm_vsweep_kernel<NV, VW, true, true>
-                    : (const void *)sgm_vsweep_kernel<NV, VW, true, false>);
+static const void *sweep_kernel(bool up, bool wta, int ns, size_t *smem_bytes) {
+  if (!up) return ns == 1 ? variant<NV, VW, false, false, 1>(smem_bytes) : variant<NV, VW, false, false, 2>(smem_bytes);
+  if (ns == 3) return wta ? variant<NV, VW, true, true, 3>(smem_bytes) : variant<NV, VW, true, false, 3>(smem_bytes);
+  return wta ? variant<NV, VW, true, true, 2>(smem_bytes) : variant<NV, VW, true, false, 2>(smem_bytes);
 }
 
+// CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.  `ns3`: the caller
+// wants the three-stream up sweep (and the overwriting down sweep) as well.
 template <int NV, int VW>
-static int ctas(int W) {
-  using C = Cfg<NV * 32 * VW>;
-  static PerDeviceInt cache;  // per instantiation and device (attribute opt-in + occupancy)
+static int ctas(int W, bool ns3) {
+  static PerDeviceInt cache[2];  // per instantiation and device (attribute opt-in + occupancy)
   const int dev = device_slot();
   int cap = 0;
-  if (!cache.get(dev, &cap)) {
+  if (!cache[ns3 ? 1 : 0].get(dev, &cap)) {
     int per_sm = 1 << 30;
-    for (int v = 0; v < 3; ++v) {
-      const void *k = sweep_kernel<NV, VW>(v > 0, v > 1);
+    for (int v = 0; v < 6; ++v) {
+      const int ns = v < 3 ? 2 : (v == 3 ? 1 : 3);
+      if (!ns3 && ns != 2) continue;
+      size_t bytes = 0;
+      const void *k = sweep_kernel<NV, VW>(v != 0 && v != 3, v == 2 || v == 5, ns, &bytes);
       int n = 0;
-      if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kBytes) != cudaSuccess ||
-          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, kThreads, C::kBytes) != cudaSuccess) {
+      if (k == nullptr) { per_sm = 0; break; }
+      if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess ||
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, kThreads, bytes) != cudaSuccess) {
         cudaGetLastError();
         return 0;
       }
       per_sm = n < per_sm ? n : per_sm;
     }
+    per_sm = per_sm > 1 ? 1 : per_sm;  // one CTA per SM: the ring is sized for it
     cap = per_sm * num_sms();
-    cache.set(dev, cap);
+    cache[ns3 ? 1 : 0].set(dev, cap);
   }
   int G = cap < kMaxCtas ? cap : kMaxCtas;
   if (G > W / 2) G = W / 2;
@@ -719,17 +762,16 @@ static int ctas(int W) {
 }
 
 template <int NV, int VW>
-static int run(const float *cost, const float *image, float *out, int32_t *disp, int H, int W, int D,
-               float p1, float p2, int min_limit, int up, bool store_vol, char *ws,
+static int run(const float *cost, const float *image, float *out, const float *extra, int32_t *disp, int H,
+               int W, int D, float p1, float p2, int min_limit, int up, bool store_vol, int ns, char *ws,
                cudaStream_t stream) {
   constexpr int DPAD = NV * 32 * VW;
-  using C = Cfg<DPAD>;
-  static_assert(C::kBytes <= 227 * 1024, "shared memory budget");
-  const void *kernel = sweep_kernel<NV, VW>(up != 0, disp != nullptr);
-  const int G = ctas<NV, VW>(W);
-  if (G < 1) return 1;
+  size_t smem_bytes = 0;
+  const void *kernel = sweep_kernel<NV, VW>(up != 0, disp != nullptr, ns, &smem_bytes);
+  const int G = ctas<NV, VW>(W, ns != 2);
+  if (G < 1 || kernel == nullptr) return 1;
   Params P;
-  P.cost = cost; P.out = out; P.disp = disp;
+  P.cost = cost; P.out = out; P.extra = extra; P.disp = disp;
   P.pen = reinterpret_cast<const float4 *>(ws + flags_and_rings_bytes(DPAD)) + (up ? (size_t)H * W : 0);
   P.xcons = reinterpret_cast<unsigned *>(ws);
   P.xring = reinterpret_cast<unsigned long long *>(ws + align256(kMaxCtas * kFlagStride * sizeof(unsigned)));
@@ -743,8 +785,7 @@ static int run(const float *cost, const float *image, float *out, int32_t *disp,
   STM_CUDA_TRY(cudaMemsetAsync(ws, 0, align256(kMaxCtas * kFlagStride * sizeof(unsigned)) +
                                           (size_t)G * kRX * 3 * DPAD * sizeof(unsigned long long), stream));
   void *args[] = {&P};
-  STM_CUDA_TRY(cudaLaunchCooperativeKernel(kernel, dim3(G), dim3(kThreads), args,
-                                           (size_t)C::kBytes, stream));
+  STM_CUDA_TRY(cudaLaunchCooperativeKernel(kernel, dim3(G), dim3(kThreads), args, smem_bytes, stream));
   return check_launch("sgm_vsweep_kernel");
 }
 
@@ -785,11 +826,11 @@ int launch_sgm_vsweep_prepare(const float *image, int H, int W, int D, float p1,
 }
 
 // Whether launch_sgm_vsweep will take this shape on the current device.
-bool sgm_vsweep_can_run(int H, int W, int D) {
+bool sgm_vsweep_can_run(int H, int W, int D, bool three_streams) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return false;
   const LaneMap m = pick_lane_map(D);
 #define STM_VSWEEP_CASE(NV_, VW_) \
-  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W) > 0;
+  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W, three_streams) > 0;
   STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
   STM_VSWEEP_CASE(1, 1)
 #undef STM_VSWEEP_CASE
@@ -799,19 +840,21 @@ bool sgm_vsweep_can_run(int H, int W, int D) {
 // One fused sweep: out += L2+L4+L6 (up = 0) or L3+L5+L7 (up = 1, reference multiplicities),
 // optionally without writing the sums back (store_vol = false) and/or emitting the disparity
 // map.  Returns 1 when the shape is not handled here (the caller runs the directions one by one).
-int launch_sgm_vsweep(const float *cost, const float *image, float *out, int32_t *disp, int H, int W,
-                      int D, float p1, float p2, int min_limit, int up, bool store_vol,
-                      void *workspace, size_t workspace_bytes, cudaStream_t stream) {
+int launch_sgm_vsweep(const float *cost, const float *image, float *out, const float *extra, int32_t *disp,
+                      int H, int W, int D, float p1, float p2, int min_limit, int up, bool store_vol,
+                      int volume_streams, void *workspace, size_t workspace_bytes, cudaStream_t stream) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return 1;
   if (workspace == nullptr || workspace_bytes < sgm_vsweep_workspace_bytes(H, W, D)) return 1;
   if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) |
-       reinterpret_cast<uintptr_t>(workspace)) & 15)
+       reinterpret_cast<uintptr_t>(workspace) | reinterpret_cast<uintptr_t>(extra)) & 15)
     return 1;
+  if (volume_streams < 1 || volume_streams > 3 || (volume_streams == 3) != (extra != nullptr)) return 1;
   const LaneMap m = pick_lane_map(D);
   char *ws = static_cast<char *>(workspace);
 #define STM_VSWEEP_CASE(NV_, VW_)      \
   if (m.NV == NV_ && m.VW == VW_)      \
-    return vsweep::run<NV_, VW_>(cost, image, out, disp, H, W, D, p1, p2, min_limit, up, store_vol, ws, stream);
+    return vsweep::run<NV_, VW_>(cost, image, out, extra, disp, H, W, D, p1, p2, min_limit, up, store_vol, \
+                                 volume_streams, ws, stream);
   STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
   STM_VSWEEP_CASE(1, 1)
 #undef STM_VSWEEP_CASE

@@ -23,6 +23,7 @@ STM_SGM_OVERWRITE = 2
 STM_SGM_FUSED_SWEEPS = 4
 STM_SGM_DISPARITY_ONLY = 8
 STM_SGM_SEQUENTIAL = 16
+STM_SGM_OVERLAP = 32
 STM_DP_CPU_EXACT = 1
 STM_TEX_F32, STM_TEX_U8 = 0, 1
 
@@ -41,6 +42,8 @@ _lib.stm_ssd_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _vp]
 _lib.stm_birchfield_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _vp]
 _lib.stm_sgm_workspace_bytes.argtypes = [_i, _i, _i]
 _lib.stm_sgm_workspace_bytes.restype = _sz
+_lib.stm_sgm_workspace_bytes_flags.argtypes = [_i, _i, _i, _u]
+_lib.stm_sgm_workspace_bytes_flags.restype = _sz
 _lib.stm_sgm_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _f, _f, _u, _vp, _sz, _vp]
 _lib.stm_wta_f32.argtypes = [_vp, _vp, _i, _i, _i, _vp]
 _lib.stm_sgm_wta_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _u, _vp, _sz, _vp]
@@ -299,7 +302,7 @@ class AggregationOps:
             raise RuntimeError("RunSemiglobal: shapes do not match")
         cost, left = cost.contiguous(), left.contiguous()
         H, W, D = cost.shape
-        nbytes = int(_lib.stm_sgm_workspace_bytes(H, W, D))
+        nbytes = int(_lib.stm_sgm_workspace_bytes_flags(H, W, D, int(flags)))
         ws = _sgm_workspace(cost.device, nbytes)
         with torch.cuda.device(cost.device):
             _check(_lib.stm_sgm_f32(cost.data_ptr(), left.data_ptr(), out.data_ptr(), H, W, D,
@@ -339,7 +342,7 @@ class AggregationOps:
             raise RuntimeError("RunSemiglobal: shapes do not match")
         cost, left = cost.contiguous(), left.contiguous()
         H, W, D = cost.shape
-        ws = _sgm_workspace(cost.device, int(_lib.stm_sgm_workspace_bytes(H, W, D)))
+        ws = _sgm_workspace(cost.device, int(_lib.stm_sgm_workspace_bytes_flags(H, W, D, int(flags))))
         with torch.cuda.device(cost.device):
             _check(_lib.stm_sgm_wta_f32(cost.data_ptr(), left.data_ptr(), out.data_ptr(),
                                         disp.data_ptr(), H, W, D, float(penalty1), float(penalty2),

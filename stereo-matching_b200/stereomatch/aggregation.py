@@ -5,7 +5,7 @@ import torch
 
 from ._common import empty_tensor
 from ._cstereomatch import (STM_SGM_MIN_ALL_D, STM_SGM_OVERWRITE, STM_SGM_FUSED_SWEEPS,
-                             STM_SGM_DISPARITY_ONLY, STM_SGM_SEQUENTIAL)
+                             STM_SGM_DISPARITY_ONLY, STM_SGM_SEQUENTIAL, STM_SGM_OVERLAP)
 from ._cstereomatch import AggregationOps as _AggregationOps
 
 
@@ -33,16 +33,21 @@ class Semiglobal:
         (where they are faster), True always, False never (reference order).
         Shapes the sweeps do not handle (more than 13 columns per SM, D not in {<=32, 64, 128,
         192, 256}) take the per-direction passes.
+      * overlap (with the fused sweeps; default on): the two horizontal passes run on a helper
+        stream next to the down sweep, which writes a workspace volume of its own that the up
+        sweep adds (STM_SGM_OVERLAP).  Costs one more volume of workspace (1.06 GB at 1080p
+        D=128); overlap=False keeps the four passes one after the other.
     """
 
     def __init__(self, penalty1: float = 0.1, penalty2: float = 0.2, *,
                  min_over_all_d: bool = False, fused_sweeps: Optional[bool] = None,
-                 concurrent_directions: bool = True):
+                 concurrent_directions: bool = True, overlap: bool = True):
         self.penalty1 = penalty1
         self.penalty2 = penalty2
         self.min_over_all_d = min_over_all_d
         self.fused_sweeps = fused_sweeps
         self.concurrent_directions = concurrent_directions
+        self.overlap = overlap
 
     def _use_fused_sweeps(self, cost_volume: torch.Tensor) -> bool:
         if self.fused_sweeps is None:
@@ -65,7 +70,7 @@ class Semiglobal:
         if not self.concurrent_directions:
             flags |= STM_SGM_SEQUENTIAL
         if self._use_fused_sweeps(cost_volume):
-            flags |= STM_SGM_FUSED_SWEEPS
+            flags |= STM_SGM_FUSED_SWEEPS | (STM_SGM_OVERLAP if self.overlap else 0)
         _AggregationOps.run_semiglobal(cost_volume, left_image, self.penalty1, self.penalty2,
                                        sga_volume, flags)
         return sga_volume
@@ -90,7 +95,7 @@ class Semiglobal:
         if not self.concurrent_directions:
             flags |= STM_SGM_SEQUENTIAL
         if self._use_fused_sweeps(cost_volume):
-            flags |= STM_SGM_FUSED_SWEEPS
+            flags |= STM_SGM_FUSED_SWEEPS | (STM_SGM_OVERLAP if self.overlap else 0)
         _AggregationOps.run_semiglobal_wta(cost_volume, left_image, self.penalty1, self.penalty2,
                                            sga_volume, disparity_img, flags)
         return sga_volume, disparity_img

@@ -122,14 +122,15 @@ def test_sgm_golden(sm, golden, case):
     (35, 13, 96, "unit", 0.3, 1.0, True), (11, 29, 20, "raw", 5.0, 9.0, False),
     (1, 9, 32, "unit", 0.1, 0.2, False), (9, 1, 32, "unit", 0.1, 0.2, False),
 ])
-@pytest.mark.parametrize("mode", ["default", "sequential", "fused_sweeps"])
+@pytest.mark.parametrize("mode", ["default", "sequential", "fused_sweeps", "fused_sweeps_no_overlap"])
 def test_sgm_vs_oracle(sm, H, W, D, scale, p1, p2, all_d, mode):
     """All SGM modes: one kernel per direction -- concurrently for these small volumes
     (default) or one after the other -- and the fused raster sweeps."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H * 7 + W, scale=scale)
     cost = O.ssd(left, right, D, 3)
     want = O.sgm(cost, left, p1, p2, min_over_all_d=all_d)
-    got = sm.aggregation.Semiglobal(p1, p2, min_over_all_d=all_d, fused_sweeps=mode == "fused_sweeps",
+    got = sm.aggregation.Semiglobal(p1, p2, min_over_all_d=all_d, fused_sweeps=mode.startswith("fused_sweeps"),
+                                    overlap=mode != "fused_sweeps_no_overlap",
                                     concurrent_directions=mode != "sequential")(cuda(cost), cuda(left))
     assert_volume_close(got, want)
 
@@ -170,8 +171,13 @@ def test_sgm_sweeps_many_ctas_and_ring_wraps(sm, H, W, D):
     assert_volume_close(got, want)
     # deterministic: a second run is bit-identical
     assert torch.equal(got, fused(c, l))
-    # and the two modes agree with each other to the same bar
+    # and the modes agree with each other to the same bar
     assert_volume_close(sm.aggregation.Semiglobal()(c, l), got.cpu().numpy())
+    plain = sm.aggregation.Semiglobal(fused_sweeps=True, overlap=False)
+    assert_volume_close(plain(c, l), want)
+    _, d_over = fused.aggregate_and_reduce(c, l, keep_volume=False)
+    _, d_plain = plain.aggregate_and_reduce(c, l, keep_volume=False)
+    assert float((d_over != d_plain).float().mean()) <= 1e-3
 
 
 def test_sgm_accumulates_like_the_reference(sm):
