@@ -16,6 +16,7 @@ char *last_error_buffer() {
 int launch_wta(const float *, int32_t *, int, int, int, cudaStream_t);
 int launch_ssd(const float *, const float *, float *, int, int, int, int, cudaStream_t);
 int launch_birchfield(const float *, const float *, float *, int, int, int, cudaStream_t);
+int launch_birchfield_wta(const float *, const float *, int32_t *, int, int, int, cudaStream_t);
 size_t sgm_workspace_bytes(int, int, int);
 size_t sgm_workspace_bytes_flags(int, int, int, unsigned);
 int sgm_pass_timing(bool);
@@ -100,6 +101,19 @@ int stm_birchfield_f32(const float *left, const float *right, float *cost, int H
   STM_REQUIRE(left && right && cost, "birchfield: null pointer");
   if ((rc = require_device())) return rc;
   return launch_birchfield(left, right, cost, H, W, D, (cudaStream_t)stream);
+}
+
+int stm_birchfield_wta_f32(const float *left, const float *right, int32_t *disparity, int H, int W, int D,
+                           void *stream) {
+  int rc = check_shape("birchfield_wta", H, W, D);
+  if (rc) return rc;
+  STM_REQUIRE(left && right && disparity, "birchfield_wta: null pointer");
+  if ((rc = require_device())) return rc;
+  rc = launch_birchfield_wta(left, right, disparity, H, W, D, (cudaStream_t)stream);
+  if (rc == 1)
+    return fail(STM_EUNSUPPORTED, "birchfield_wta: needs D %% 64 == 0 and 8 <= W <= ~6000 (got W=%d D=%d); "
+                "use stm_birchfield_f32 + stm_wta_f32", W, D);
+  return rc;
 }
 
 size_t stm_sgm_workspace_bytes(int H, int W, int D) {

@@ -142,10 +142,15 @@ __device__ __forceinline__ u64 add2(u64 a, u64 b) {
 }
 }  // namespace bt2
 
-template <int NJ>
+// WTA = true: the volume is never written.  The warp that produced a pixel's D costs holds them
+// (4 per lane at D = 128), so it takes the argmin itself -- first (lowest-d) minimum, NaN never
+// wins, NaN at d = 0 -> 0, the rule of wta.cu / reference src/winners_take_all.cu:21-40 -- and writes
+// 4 bytes per pixel instead of 4 bytes per pixel-disparity (cost + reduce of a
+// pipeline without aggregation in one kernel).
+template <int NJ, bool WTA>
 __global__ void __launch_bounds__(256)
 birchfield_row_packed_kernel(const float *__restrict__ left, const float *__restrict__ right,
-                             float *__restrict__ cost, int H, int W) {
+                             float *__restrict__ cost, int32_t *__restrict__ disp, int H, int W) {
   using namespace bt2;
   static_assert(NJ % 2 == 0, "disparity groups are processed in pairs");
   constexpr int D = 32 * NJ, NP = NJ / 2;
@@ -198,14 +203,19 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
 #pragma unroll
   for (int k = 0; k < 7; ++k) eval(xa - 4 + k, win[(k + 4) & 7]);
 
-  float *orow = cost + ((size_t)y * W + xa) * D + lane;
+  float *orow = WTA ? nullptr : cost + ((size_t)y * W + xa) * D + lane;
+  int32_t *drow = WTA ? disp + (size_t)y * W : nullptr;
   auto block8 = [&](auto edge_tag, auto tail_tag, int x0) {
     constexpr bool EDGE = decltype(edge_tag)::value, TAIL = decltype(tail_tag)::value;
+    int mine = 0;  // WTA: lane u keeps the disparity of column x0 + u
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       const int x = x0 + u;
       if (!TAIL || x < xb) {  // warp-uniform
         eval(x + 3, win[(u + 3) & 7]);
+        float best = CUDART_INF_F;  // WTA: this lane's minimum over its NJ disparities ...
+        int best_d = 0x7fffffff;    // ... and the lowest d that attains it
+        bool nan_at_0 = false;
 #pragma unroll
         for (int q = 0; q < NP; ++q) {
           u64 s = win[(u + 4) & 7][q];  // p = x-4, then x-3 .. x+3 left to right
@@ -217,12 +227,32 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
             if (lane + 64 * q > x) s0 = CUDART_INF_F;
             if (lane + 64 * q + 32 > x) s1 = CUDART_INF_F;
           }
-          __stcs(orow + u * D + 64 * q, s0);
-          __stcs(orow + u * D + 64 * q + 32, s1);
+          if constexpr (!WTA) {
+            __stcs(orow + u * D + 64 * q, s0);
+            __stcs(orow + u * D + 64 * q + 32, s1);
+          } else {
+            // ascending d within the lane, strict <: the lowest d of equal values sticks; NaN never passes
+            if (q == 0) nan_at_0 = s0 != s0;
+            if (s0 < best) { best = s0; best_d = lane + 64 * q; }
+            if (s1 < best) { best = s1; best_d = lane + 64 * q + 32; }
+          }
+        }
+        if constexpr (WTA) {
+          float m;  // warp minimum (redux.sync.min.f32 returns the non-NaN operand), then the lowest d equal to it
+          asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(m) : "f"(best));
+          unsigned idx = (best == m) ? (unsigned)best_d : 0x7fffffffu;
+          idx = __reduce_min_sync(FULL, idx);
+          const bool nan0 = __shfl_sync(FULL, nan_at_0 ? 1 : 0, 0) != 0;
+          const int w = (nan0 || idx == 0x7fffffffu) ? 0 : (int)idx;
+          if (lane == u) mine = w;
         }
       }
     }
-    orow += 8 * D;
+    if constexpr (WTA) {
+      if (lane < 8 && x0 + lane < xb) drow[x0 + lane] = mine;
+    } else {
+      orow += 8 * D;
+    }
   };
   int x0 = xa;
   for (; x0 + 8 <= xb && x0 < D; x0 += 8) block8(std::true_type{}, std::false_type{}, x0);
@@ -230,15 +260,28 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
   if (x0 < xb) block8(std::true_type{}, std::true_type{}, x0);
 }
 
-template <int NJ>
-static int run_birchfield_packed(const float *left, const float *right, float *cost, int H, int W,
-                                 cudaStream_t stream) {
+template <int NJ, bool WTA>
+static int run_birchfield_packed(const float *left, const float *right, float *cost, int32_t *disp, int H,
+                                 int W, cudaStream_t stream) {
   const size_t smem = (size_t)(2 * W + 32 * NJ + 16) * sizeof(float4);
-  auto kernel = birchfield_row_packed_kernel<NJ>;
+  auto kernel = birchfield_row_packed_kernel<NJ, WTA>;
   if (smem > 48 * 1024)  // per device and cheap: set on every call (stm_common.cuh, per-device state)
     STM_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kernel<<<H, 256, smem, stream>>>(left, right, cost, H, W);
+  kernel<<<H, 256, smem, stream>>>(left, right, cost, disp, H, W);
   return check_launch("birchfield_row_packed_kernel");
+}
+
+// Birchfield cost + winner-takes-all without the volume.  Returns 1 when the shape is not handled.
+int launch_birchfield_wta(const float *left, const float *right, int32_t *disp, int H, int W, int D,
+                          cudaStream_t stream) {
+  if (D % 64 != 0 || W < 8 || (size_t)(2 * W + D + 16) * sizeof(float4) > 200 * 1024) return 1;
+  switch (D / 32) {
+    case 2: return run_birchfield_packed<2, true>(left, right, nullptr, disp, H, W, stream);
+    case 4: return run_birchfield_packed<4, true>(left, right, nullptr, disp, H, W, stream);
+    case 6: return run_birchfield_packed<6, true>(left, right, nullptr, disp, H, W, stream);
+    case 8: return run_birchfield_packed<8, true>(left, right, nullptr, disp, H, W, stream);
+    default: return 1;
+  }
 }
 
 template <int NJ>
@@ -260,10 +303,10 @@ int launch_birchfield_tiled(const float *left, const float *right, float *cost, 
       !((reinterpret_cast<uintptr_t>(cost)) & 3)) {
     static const char *off = getenv("STM_DEBUG_BT_PACKED");  // developer knob: "0" = kernel above
     if (!(off && off[0] == '0')) switch (D / 32) {
-      case 2: return run_birchfield_packed<2>(left, right, cost, H, W, stream);
-      case 4: return run_birchfield_packed<4>(left, right, cost, H, W, stream);
-      case 6: return run_birchfield_packed<6>(left, right, cost, H, W, stream);
-      case 8: return run_birchfield_packed<8>(left, right, cost, H, W, stream);
+      case 2: return run_birchfield_packed<2, false>(left, right, cost, nullptr, H, W, stream);
+      case 4: return run_birchfield_packed<4, false>(left, right, cost, nullptr, H, W, stream);
+      case 6: return run_birchfield_packed<6, false>(left, right, cost, nullptr, H, W, stream);
+      case 8: return run_birchfield_packed<8, false>(left, right, cost, nullptr, H, W, stream);
       default: break;
     }
   }

@@ -6,13 +6,17 @@ namespace stm {
 int launch_ssd_generic(const float *, const float *, float *, int, int, int, int, cudaStream_t);
 int launch_birchfield_generic(const float *, const float *, float *, int, int, int, cudaStream_t);
 int launch_ssd_tiled(const float *, const float *, float *, int, int, int, int, cudaStream_t);
+int launch_ssd_rows(const float *, const float *, float *, int, int, int, int, cudaStream_t);
 int launch_birchfield_tiled(const float *, const float *, float *, int, int, int, cudaStream_t);
 
 int launch_ssd(const float *left, const float *right, float *cost, int H, int W, int D, int k,
                cudaStream_t stream) {
   // tiled separable kernel for the window sizes it is instantiated for; returns 1 when it
   // does not handle `k` (then the straightforward kernel runs instead)
-  const int rc = launch_ssd_tiled(left, right, cost, H, W, D, k, stream);
+  // horizontal-first packed kernel (ssd_rows.cu) for k = 7 / 3 and D % 4 == 0, then the older tiled one
+  int rc = launch_ssd_rows(left, right, cost, H, W, D, k, stream);
+  if (rc != 1) return rc;
+  rc = launch_ssd_tiled(left, right, cost, H, W, D, k, stream);
   if (rc != 1) return rc;
   return launch_ssd_generic(left, right, cost, H, W, D, k, stream);
 }

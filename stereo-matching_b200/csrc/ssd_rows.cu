@@ -1,0 +1,340 @@
+// ssd_rows.cu -- SSD cost volume, horizontal sums first, packed arithmetic (sm_100a).
+//
+// Same function as ssd_tiled.cu (reference src/ssd.cu:31-61: C[y,x,d] = sum over the 2K x 2K window of
+// (L[r,c] - R[r,c-d])^2, clipped to the image, +inf for d > x) and the same add-only van Herk /
+// Gil-Werman sums (no subtraction: bit-exact for integer-valued images, a few ulp otherwise).
+// ncu of ssd_tiled_kernel at 1080p D=128 (profiles/r02_v2_ncu_full_summary.txt): 22 warp
+// instructions per 128-byte store, 57 % of the issue slots busy, a third of all warp samples at the
+// barrier between its two warp roles -- 0.36 ms where the store stream alone needs ~0.17.  Doubling
+// the horizontal warps bought 4 %: the kernel has too many instructions, not too few warps.
+//
+// Here the order of the two 1-D sums is swapped and everything is packed (add/sub/mul.rn.f32x2):
+//  * H warps: lane = disparity, a work item = (a PAIR of image rows, a run of 2K output columns).
+//    The two rows are staged INTERLEAVED in shared memory (float2 per column), so one 8-byte load
+//    fetches L (broadcast) or R (one per lane) of both rows and every operation of the item is a
+//    packed pair: 27 squared differences, the prefix/suffix blocks, 2K window sums per row.
+//  * V threads: thread = (output column, 4 consecutive disparities).  It reads the horizontal sums
+//    of a row as one float4, advances the vertical van Herk ring held in registers (a group of rows
+//    IS a van Herk block of 2K rows, so all ring indices are static) and writes 16 bytes of C with a
+//    streaming store; 8 threads write one pixel's 128-byte chunk.
+// The two roles work on consecutive groups through a double-buffered tile and meet at one barrier
+// per group; image rows are requested with cp.async two groups ahead.  HBM traffic = the 4 B/pix-disp
+// store of C plus the images.
+//
+// What was measured (1080p D=128, profiles/r02_v6_ssd_investigation.md): 0.350 ms against 0.371 for
+// ssd_tiled_kernel -- a small gain for a kernel with far fewer arithmetic instructions, because
+// instruction issue was not the limit after all.  A store-only kernel with exactly this write
+// pattern (128-byte chunks of each pixel's vector from four CTAs) runs in 0.164 ms, so the pattern
+// is not the limit either.  What is left is the single CTA per SM (174 KB of shared memory) with
+// its two roles meeting at a barrier, and ~2700 shared-memory wavefronts per group.  Variants that
+// were measured and are worse: plain instead of streaming stores (0.43), 11 H warps (0.46, spills),
+// V warps helping with H items (0.61, spills).
+#include <cstdlib>
+
+#include "stm_common.cuh"
+
+#ifndef STM_SSD_NH7
+#define STM_SSD_NH7 7   /* 11 H warps: 80-register cap, spills, 0.36 -> 0.46 ms (measured) */
+#endif
+
+namespace stm {
+namespace ssdr {
+
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk(float a, float b) {
+  u64 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void upk(u64 r, float &a, float &b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r));
+}
+__device__ __forceinline__ u64 add2(u64 a, u64 b) {
+  u64 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) {
+  u64 d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+  u64 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+template <int K, int RUNS, int NH>
+struct Cfg {
+  static constexpr int WIN = 2 * K;            // window, van Herk block, rows per group
+  static constexpr int PAIRS = WIN / 2;        // row pairs per group
+  static constexpr int TX = RUNS * WIN;        // output columns per CTA
+  static constexpr int TXH = TX + WIN - 1;     // staged left columns (halo)
+  static constexpr int DC = 32;                // disparities per CTA
+  static constexpr int RROW = TXH + DC - 1;    // staged right columns
+  static constexpr int VTHREADS = ((TX * 8 + 31) / 32) * 32;
+  static constexpr int THREADS = VTHREADS + NH * 32;
+  static constexpr int ITEMS = PAIRS * RUNS;   // item-pairs per group
+  // The V warps have ~1/3 of an H warp's instructions per group: each of the first V_ITEMS of them
+  // also takes one item, so that both roles reach the barrier at about the same time.
+  // (measured: with V_ITEMS = ITEMS / 3 the V role spills and becomes the critical path, 0.36 -> 0.61 ms)
+  static constexpr int V_ITEMS = 0;
+  static constexpr int H_ITEMS = ITEMS - V_ITEMS;
+  // shared memory, in floats: hbuf[2][WIN][TX][DC], rows[3][PAIRS][TXH + RROW] float2
+  static constexpr int HBUF = WIN * TX * DC;
+  static constexpr int ROWBUF = PAIRS * (TXH + RROW) * 2;
+  static constexpr size_t SMEM = (size_t)(2 * HBUF + 3 * ROWBUF) * sizeof(float);
+};
+
+__device__ __forceinline__ void named_barrier(int threads) {
+  asm volatile("bar.sync 1, %0;" ::"r"(threads) : "memory");
+}
+
+}  // namespace ssdr
+
+// One horizontal work item: row pair p, run q of group buffer `rb` -> horizontal sums in `hb`.
+template <int K, int RUNS, int NH>
+__device__ __forceinline__ void ssd_rows_item(const float2 *rb, float *hb, int item, int lane, int x0, int d0, int W) {
+  using namespace ssdr;
+  using C = Cfg<K, RUNS, NH>;
+  constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
+  const int dglob = d0 + lane;
+  const int p = item / RUNS, q = item - p * RUNS;
+  const float2 *lp = rb + p * (TXH + RROW) + q * WIN;                          // + k
+  const float2 *rp = rb + p * (TXH + RROW) + TXH + q * WIN + (DC - 1) - lane;  // + k
+  const int c0 = x0 + q * WIN - K;  // image column of k = 0
+  // warp-uniform: every column of the item lies in [0, W) and right of every disparity
+  const bool interior = c0 >= d0 + DC - 1 && c0 + 2 * WIN - 2 < W;
+  u64 v[2 * WIN - 1];  // (row 2p, row 2p+1) squared differences of column k
+#pragma unroll
+  for (int k = 0; k < 2 * WIN - 1; ++k) {
+    const u64 l2 = *reinterpret_cast<const u64 *>(lp + k);
+    const u64 r2 = *reinterpret_cast<const u64 *>(rp + k);
+    const u64 df = sub2(l2, r2);
+    v[k] = mul2(df, df);
+  }
+  if (!interior) {
+#pragma unroll
+    for (int k = 0; k < 2 * WIN - 1; ++k) {
+      const int c = c0 + k;
+      if (!(c < W && c - dglob >= 0)) v[k] = 0ull;  // window clipped to [d, W) (reference :40-42)
+    }
+  }
+  // suffix sums of block A = v[0..WIN), prefix sums of block B = v[WIN..2WIN-1)
+#pragma unroll
+  for (int i = WIN - 2; i >= 0; --i) v[i] = add2(v[i], v[i + 1]);
+#pragma unroll
+  for (int i = WIN + 1; i < 2 * WIN - 1; ++i) v[i] = add2(v[i], v[i - 1]);
+  float *o0 = hb + ((size_t)(2 * p) * TX + q * WIN) * DC + lane;
+  float *o1 = o0 + (size_t)TX * DC;
+#pragma unroll
+  for (int j = 0; j < WIN; ++j) {
+    float s0, s1;
+    upk(j == 0 ? v[0] : add2(v[j], v[WIN + j - 1]), s0, s1);
+    o0[j * DC] = s0;
+    o1[j * DC] = s1;
+  }
+}
+
+template <int K, int RUNS, int NH>
+__global__ void __launch_bounds__(ssdr::Cfg<K, RUNS, NH>::THREADS, 1)
+ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right, float *__restrict__ cost,
+                int H, int W, int D, int rows_per_chunk, int d_fastest, int store_policy) {
+  using namespace ssdr;
+  using C = Cfg<K, RUNS, NH>;
+  constexpr int WIN = C::WIN, PAIRS = C::PAIRS, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
+  extern __shared__ __align__(16) float smem[];
+  float *hbuf = smem;                 // [(b*WIN + row)*TX + x][DC]
+  float *rows = smem + 2 * C::HBUF;   // [b3][pair][TXH + RROW] float2: left columns, then right columns
+
+  const int tid = threadIdx.x;
+  const int x0 = (d_fastest ? blockIdx.y : blockIdx.x) * TX;
+  const int d0 = (d_fastest ? blockIdx.x : blockIdx.y) * DC;
+  const int ya = blockIdx.z * rows_per_chunk;
+  const int yb = min(H, ya + rows_per_chunk);
+  const int T = (yb - ya) + WIN - 1;          // input rows ya-K .. yb+K-2
+  const int n_groups = (T + WIN - 1) / WIN;
+  const int cbase = x0 - K;                   // image column of staged left column 0
+  const int ubase = cbase - d0 - (DC - 1);    // image column of staged right column 0
+
+  if (tid < C::VTHREADS) {
+    // ------------------------------------------------------------------ V role (+ staging)
+    // Rows of group g: image rows ya - K + g*WIN + i, i = 0..WIN-1, interleaved in pairs; pixels
+    // outside the image are zero-filled by a source size of 0 (the address is clamped to stay valid).
+    // A thread copies the same (row-in-group, column) elements in every group: their source column
+    // pointer, destination offset and column validity are worked out once (the first version did
+    // the index arithmetic per element and group: 47 instructions per 4 bytes, a quarter of the
+    // kernel's instructions).
+    constexpr int ROWLEN = TXH + RROW, NE = (WIN * ROWLEN + C::VTHREADS - 1) / C::VTHREADS;
+    const float *st_col[NE];   // column pointer in image row 0
+    int st_i[NE];              // row within the group; -1: no element (tail) or column outside the image
+    uint32_t st_dst[NE];       // byte offset in a rows buffer
+#pragma unroll
+    for (int e = 0; e < NE; ++e) {
+      const int idx = tid + e * C::VTHREADS;
+      const int i = idx / ROWLEN, col = idx - i * ROWLEN;
+      const bool is_left = col < TXH;
+      const int c = is_left ? cbase + col : ubase + (col - TXH);
+      st_col[e] = (is_left ? left : right) + min(max(c, 0), W - 1);
+      st_i[e] = (idx < WIN * ROWLEN && c >= 0 && c < W) ? i : -1 - i;  // negative: zero-fill (i = -1 - st_i)
+      st_dst[e] = idx < WIN * ROWLEN ? (uint32_t)((((i >> 1) * ROWLEN + col) * 2 + (i & 1)) * sizeof(float)) : 0xffffffffu;
+    }
+    const uint32_t rows_s = (uint32_t)__cvta_generic_to_shared(rows);
+    auto stage_group = [&](int g) {
+      const uint32_t dst0 = rows_s + (uint32_t)((g % 3) * C::ROWBUF * sizeof(float));
+      const int r0 = ya - K + g * WIN;
+#pragma unroll
+      for (int e = 0; e < NE; ++e) {
+        if (st_dst[e] != 0xffffffffu) {
+          const int i = st_i[e] >= 0 ? st_i[e] : -1 - st_i[e];
+          const int r = r0 + i;
+          const int ok_bytes = (st_i[e] >= 0 && r >= 0 && r < H) ? 4 : 0;
+          const float *src = st_col[e] + (size_t)min(max(r, 0), H - 1) * W;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + st_dst[e]), "l"(src), "r"(ok_bytes) : "memory");
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    stage_group(0);
+    stage_group(1);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    named_barrier(C::THREADS);  // group 0's rows are in shared memory
+
+    const int xl = tid >> 3, dq = tid & 7;
+    const int x = x0 + xl;
+    const bool active = xl < TX && x < W;
+    const int dfirst = d0 + 4 * dq;
+    const bool plain = active && dfirst + 3 < D && dfirst + 3 <= x;   // nothing to test per element
+    float ring[WIN][4];
+    float pre[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < WIN; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ring[i][j] = 0.f;
+    float *ocol = cost + ((size_t)x * D + dfirst);   // + y * W * D
+
+    for (int g = 0; g <= n_groups; ++g) {
+      stage_group(g + 2);
+      if (g >= 1 && active) {
+        const float *hb = hbuf + (size_t)(((g - 1) & 1) * C::HBUF) + (size_t)xl * DC + 4 * dq;
+        const int ybase = ya - WIN + 1 + (g - 1) * WIN;  // output row completed by row 0 of the group
+#pragma unroll
+        for (int i = 0; i < WIN; ++i) {
+          const float4 h = *reinterpret_cast<const float4 *>(hb + (size_t)i * TX * DC);
+          const float hv[4] = {h.x, h.y, h.z, h.w};
+          float out[4];
+#pragma unroll
+          for (int j = 0; j < 4; j += 2) {
+            u64 p2 = add2(pk(pre[j], pre[j + 1]), pk(hv[j], hv[j + 1]));
+            upk(p2, pre[j], pre[j + 1]);
+            if (i < WIN - 1) p2 = add2(p2, pk(ring[i + 1][j], ring[i + 1][j + 1]));
+            upk(p2, out[j], out[j + 1]);
+            ring[i][j] = hv[j];
+            ring[i][j + 1] = hv[j + 1];
+          }
+          const int y = ybase + i;
+          if (y >= ya && y < yb) {  // block-uniform
+            float *o = ocol + (size_t)y * W * D;
+            if (plain) {
+              const float4 o4 = make_float4(out[0], out[1], out[2], out[3]);
+              if (store_policy == 0) __stcs(reinterpret_cast<float4 *>(o), o4);
+              else if (store_policy == 1) *reinterpret_cast<float4 *>(o) = o4;
+              else __stwt(reinterpret_cast<float4 *>(o), o4);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (dfirst + j < D) __stcs(o + j, dfirst + j > x ? CUDART_INF_F : out[j]);
+            }
+          }
+        }
+        // the finished block of raw values becomes suffix sums; the prefix restarts
+#pragma unroll
+        for (int i = WIN - 2; i >= 1; --i)
+#pragma unroll
+          for (int j = 0; j < 4; j += 2) {
+            const u64 s2 = add2(pk(ring[i][j], ring[i][j + 1]), pk(ring[i + 1][j], ring[i + 1][j + 1]));
+            upk(s2, ring[i][j], ring[i][j + 1]);
+          }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) pre[j] = 0.f;
+      }
+      if (C::V_ITEMS > 0 && g < n_groups && (tid >> 5) < C::V_ITEMS)
+        ssd_rows_item<K, RUNS, NH>(reinterpret_cast<const float2 *>(rows + (g % 3) * C::ROWBUF),
+                                   hbuf + (size_t)((g & 1) * C::HBUF), C::H_ITEMS + (tid >> 5), tid & 31, x0, d0, W);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      named_barrier(C::THREADS);
+    }
+  } else {
+    // ------------------------------------------------------------------ H role
+    const int hw = (tid - C::VTHREADS) >> 5, lane = tid & 31;
+    named_barrier(C::THREADS);  // group 0's rows are in shared memory
+    for (int g = 0; g <= n_groups; ++g) {
+      if (g < n_groups) {
+        const float2 *rb = reinterpret_cast<const float2 *>(rows + (g % 3) * C::ROWBUF);
+        float *hb = hbuf + (size_t)((g & 1) * C::HBUF);
+        // items [0, H_ITEMS) belong to the H warps; the V warps take the rest after their own rows
+        for (int item = hw; item < C::H_ITEMS; item += NH)
+          ssd_rows_item<K, RUNS, NH>(rb, hb, item, lane, x0, d0, W);
+      }
+      named_barrier(C::THREADS);
+    }
+  }
+}
+
+template <int K, int RUNS, int NH>
+static int run_ssd_rows(const float *left, const float *right, float *cost, int H, int W, int D,
+                        cudaStream_t stream) {
+  using C = ssdr::Cfg<K, RUNS, NH>;
+  static PerDeviceInt configured;  // the > 48 KB opt-in is per function AND per device
+  const int dev = device_slot();
+  int done = 0;
+  if (!configured.get(dev, &done)) {
+    if (cudaFuncSetAttribute(ssd_rows_kernel<K, RUNS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)C::SMEM) != cudaSuccess) {
+      cudaGetLastError();
+      return 1;  // the caller runs ssd_tiled_kernel
+    }
+    configured.set(dev, 1);
+  }
+  const int nx = (W + C::TX - 1) / C::TX;
+  const int nd = (D + C::DC - 1) / C::DC;
+  // Row chunks of m*WIN - (WIN-1) output rows: such a chunk reads exactly m groups of WIN input
+  // rows.  ~128 rows per chunk as in ssd_tiled.cu (many short CTAs balance over the SMs and
+  // spread the store stream); small images: at least one CTA per SM while a chunk keeps >= 2 groups.
+  int m = 20;  // 1080p D=128: 0.423 ms with 5 groups per chunk, 0.360 with 10, 0.350 with 20 (measured)
+  {
+    static const char *force = getenv("STM_DEBUG_SSD_GROUPS");  // developer knob: groups per chunk
+    if (force && atoi(force) > 0) m = atoi(force);
+  }
+  while (m > 2 && (long long)nx * nd * ((H + (m * C::WIN - C::WIN + 1) - 1) / (m * C::WIN - C::WIN + 1)) < num_sms()) --m;
+  const int rows = m * C::WIN - (C::WIN - 1);
+  const int ny = (H + rows - 1) / rows;
+  if (nd > 65535 || ny > 65535) return fail(STM_EUNSUPPORTED, "ssd: shape too large");
+  static const char *order = getenv("STM_DEBUG_SSD_ORDER");  // developer knob: "x" = x strips fastest
+  const int d_fastest = !(order && order[0] == 'x');
+  if (nx > 65535) return fail(STM_EUNSUPPORTED, "ssd: shape too large");
+  const dim3 grid = d_fastest ? dim3(nd, nx, ny) : dim3(nx, nd, ny);
+  static const char *pol = getenv("STM_DEBUG_SSD_STORE");  // developer knob: 0 = .cs (default), 1 = plain, 2 = .wt
+  const int store_policy = pol ? atoi(pol) : 0;
+  ssd_rows_kernel<K, RUNS, NH><<<grid, C::THREADS, C::SMEM, stream>>>(left, right, cost, H, W, D, rows, d_fastest,
+                                                                        store_policy);
+  return check_launch("ssd_rows_kernel");
+}
+
+// Returns 0 on success, 1 when the shape is not handled here (the caller runs ssd_tiled_kernel).
+int launch_ssd_rows(const float *left, const float *right, float *cost, int H, int W, int D, int k,
+                    cudaStream_t stream) {
+  if (D % 4 != 0 || (reinterpret_cast<uintptr_t>(cost) & 15)) return 1;  // 16-byte stores
+  {
+    static const char *off = getenv("STM_DEBUG_SSD_ROWS");  // developer knob: "0" disables
+    if (off && off[0] == '0') return 1;
+  }
+  switch (k) {
+    case 7: return run_ssd_rows<7, 3, STM_SSD_NH7>(left, right, cost, H, W, D, stream);
+    case 3: return run_ssd_rows<3, 8, 8>(left, right, cost, H, W, D, stream);
+    default: return 1;
+  }
+}
+
+}  // namespace stm

@@ -40,6 +40,8 @@ _lib.stm_last_error.restype = ctypes.c_char_p
 _lib.stm_launch_count.restype = ctypes.c_ulonglong
 _lib.stm_ssd_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _vp]
 _lib.stm_birchfield_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _vp]
+_lib.stm_birchfield_wta_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _vp]
+_lib.stm_birchfield_wta_f32.restype = _i
 _lib.stm_sgm_workspace_bytes.argtypes = [_i, _i, _i]
 _lib.stm_sgm_workspace_bytes.restype = _sz
 _lib.stm_sgm_workspace_bytes_flags.argtypes = [_i, _i, _i, _u]
@@ -286,6 +288,28 @@ class CostOps:
         with torch.cuda.device(left.device):
             _check(_lib.stm_birchfield_f32(left.data_ptr(), right.data_ptr(), cost.data_ptr(), H, W,
                                            cost.shape[2], _stream()))
+
+
+    @staticmethod
+    def compute_birchfield_wta(left_image, right_image, disparity_image, max_disparity: int) -> bool:
+        """New: compute_birchfield + run_winners_take_all in one kernel, the volume never written
+        (include/stm_abi.h, stm_birchfield_wta_f32).  Returns False when the shape is not supported
+        (D % 64 != 0 ...): the caller then runs the two stages."""
+        left = _gpu("BirchfieldKernel: left_image", left_image, torch.float32, 2)
+        right = _gpu("BirchfieldKernel: right_image", right_image, torch.float32, 2, left)
+        disp = _out("disparity_image",
+                    _gpu("RunWinnersTakeAll: disparity_image", disparity_image, torch.int32, 2, left))
+        if right.shape != left.shape or disp.shape != left.shape:
+            raise RuntimeError("BirchfieldKernel: image / disparity shapes do not match")
+        left, right = left.contiguous(), right.contiguous()
+        H, W = left.shape
+        with torch.cuda.device(left.device):
+            rc = _lib.stm_birchfield_wta_f32(left.data_ptr(), right.data_ptr(), disp.data_ptr(), H, W,
+                                             int(max_disparity), _stream())
+        if rc == -3:   # STM_EUNSUPPORTED
+            return False
+        _check(rc)
+        return True
 
 
 class AggregationOps:

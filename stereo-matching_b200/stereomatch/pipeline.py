@@ -4,7 +4,7 @@ from typing import Callable, Optional
 import torch
 
 from .aggregation import Semiglobal
-from .cost import SSDTexture
+from .cost import Birchfield, SSDTexture
 from .cuda_texture import CUDATexture
 from .disparity_reduce import WinnerTakesAll
 
@@ -41,6 +41,9 @@ class Pipeline:
         # New: Semiglobal followed by WinnerTakesAll runs as one native call (the argmin is
         # folded into the last aggregation pass).  Set to False for two separate stages.
         self.fuse_aggregation_and_reduce = True
+        # New: Birchfield followed directly by WinnerTakesAll (no aggregation) runs as one kernel that
+        # never writes the cost volume (`_cost_volume` stays None then).  Set to False for two stages.
+        self.fuse_cost_and_reduce = True
         # The aggregated volume never leaves the pipeline, so the fused call may skip writing it
         # (its buffer is scratch then).  Set to True to find the aggregation in
         # `_aggregation_volume` after estimate().
@@ -48,6 +51,13 @@ class Pipeline:
 
     def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor) -> torch.Tensor:
         """[H,W] left/right images (CUDA float32) -> int32 [H,W] disparity map."""
+        if (self.fuse_cost_and_reduce and self.aggregation is None and type(self.cost) is Birchfield
+                and type(self.disparity_reduce) is WinnerTakesAll):
+            # cost + reduce in one kernel, the volume never materialised (stm_birchfield_wta_f32)
+            fused = self.cost.cost_and_reduce(left_image, right_image, self._disparity_image)
+            if fused is not None:
+                self._disparity_image = fused
+                return fused
         self._cost_volume = self.cost(left_image, right_image, cost_volume=self._cost_volume)
         if self.aggregation is not None:
             own = self._aggregation_volume

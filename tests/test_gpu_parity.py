@@ -574,3 +574,31 @@ def test_full_height_sgm_column_strip_vs_oracle(sm, fused_sweeps):
     cost = O.ssd(left, right, D, 3)
     got = sgm(cuda(cost), cuda(left))
     assert_volume_close(got, O.sgm(cost, left, 0.1, 0.2))
+
+
+@pytest.mark.parametrize("H,W,D,scale", [(21, 45, 64, "unit"), (12, 150, 128, "unit"), (8, 70, 192, "raw"),
+                                          (4, 203, 256, "unit"), (30, 9, 64, "raw"), (1080, 1920, 128, "raw")])
+def test_birchfield_with_winner_takes_all_folded_in(sm, H, W, D, scale):
+    """stm_birchfield_wta_f32: the map is EXACTLY WinnerTakesAll of the Birchfield volume (same
+    kernel arithmetic, first-minimum rule, +inf for d > x), without the volume being written;
+    Pipeline(Birchfield, WinnerTakesAll) takes that path and leaves no cost volume behind."""
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=3 * H + W, scale=scale)
+    l, r = cuda(left), cuda(right)
+    bt = sm.cost.Birchfield(D)
+    want = sm.disparity_reduce.WinnerTakesAll()(bt(l, r))
+    got = bt.cost_and_reduce(l, r)
+    assert got is not None and got.dtype == torch.int32
+    assert torch.equal(got, want)
+    if H * W * D < 4_000_000:
+        assert np.array_equal(got.cpu().numpy(), O.wta(O.birchfield(left, right, D)))
+    pipe = sm.Pipeline(sm.cost.Birchfield(D), sm.disparity_reduce.WinnerTakesAll())
+    assert torch.equal(pipe.estimate(l, r), want) and pipe._cost_volume is None
+    pipe.fuse_cost_and_reduce = False
+    assert torch.equal(pipe.estimate(l, r), want) and pipe._cost_volume is not None
+    # a tie-heavy pair: constant images make every cost 0 -> lowest d wins everywhere
+    z = torch.full((H, W), 7.0, device="cuda")
+    assert int(bt.cost_and_reduce(z, z).max()) == 0
+    # unsupported D falls back inside Pipeline
+    assert sm.cost.Birchfield(48).cost_and_reduce(l, r) is None
+    p48 = sm.Pipeline(sm.cost.Birchfield(48), sm.disparity_reduce.WinnerTakesAll())
+    assert torch.equal(p48.estimate(l, r), sm.disparity_reduce.WinnerTakesAll()(sm.cost.Birchfield(48)(l, r)))
