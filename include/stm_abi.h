@@ -55,8 +55,9 @@ extern "C" {
                                    256}, unaligned pointers) run the per-direction passes. */
 #define STM_SGM_DISPARITY_ONLY 8u /* stm_sgm_wta_f32 only: `out` is scratch.  The last pass reduces
                                      the finished sums to the disparity map without writing them
-                                     back (4 B/pix-disp less HBM traffic); on return `out` holds
-                                     the sum of the first seven directions, not the result. */
+                                     back (4 B/pix-disp less HBM traffic); on return the content
+                                     of `out` is UNSPECIFIED (partial sums that depend on the
+                                     schedule), only `disparity` is a result. */
 #define STM_SGM_SEQUENTIAL 16u /* always run the eight direction passes one after the other.  Without
                                   it, landscape / square volumes of at most 48 MB (latency-bound,
                                   L2-resident: BASELINE.json config 2) run the eight directions
@@ -72,9 +73,15 @@ extern "C" {
                                when the shape or the workspace does not allow it.  Sum associated
                                ((L0 + L1) + (L2+L4+L6)) + L3 + L5 + L7: within 1e-4, not bit-identical. */
 
-/* flags of stm_dp_f32 */
-#define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68);
-                               requires D <= H <= W and a zeroed path volume */
+/* flags of stm_dp_f32.  The DEFAULT mode (no flag) is a defined variant: the reference CUDA functor
+ * (src/dynamic_programming.cu:83-130) with its shared-memory race resolved read-before-write.  It
+ * equals the reference CUDA kernel bit for bit where that kernel is race-free (D <= 32, tested on
+ * the box against the compiled reference) and is otherwise pinned only by the oracle's restatement;
+ * it is a different algorithm from the CPU functor (a few % of pixels differ). */
+#define STM_DP_CPU_EXACT 1u /* literal reference CPU functor (src/dynamic_programming.cu:24-68),
+                               bit-identical to the compiled reference CPU op; requires
+                               D <= H <= W and a zeroed path volume; serial in d (slow: ~80 ms
+                               at 1080p D=128 against 0.32 ms for the default mode) */
 
 /* Library / build identification, e.g. "stm_b200 0.1 sm_100a". */
 const char *stm_version(void);

@@ -788,7 +788,9 @@ static int sgm_fused_overlap(const float *cost, const float *image, float *out, 
   int rc = aux_streams(&aux);
   if (rc) return rc;
   std::lock_guard<std::mutex> enqueue_lock(aux->mu);  // fork ... join is one critical section
-  cudaStream_t helper = aux->stream[0];
+  // callers on different streams (two frames in flight, stereomatch.streaming) get different helpers
+  const int hi = (int)((reinterpret_cast<uintptr_t>(stream) >> 6) % 7u);
+  cudaStream_t helper = aux->stream[hi];
   const unsigned mode0 = (flags & STM_SGM_OVERWRITE) ? 0u : kSgmAccumulate;
   const bool store_up = !(disp && (flags & STM_SGM_DISPARITY_ONLY));
   pass_mark(0, 8, stream);
@@ -804,7 +806,7 @@ static int sgm_fused_overlap(const float *cost, const float *image, float *out, 
       return rc;
     if ((rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 1, 0, H, min_limit, kSgmAccumulate, nullptr, -1, helper)))
       return rc;
-    if (cudaEventRecord(aux->join[0], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[0], 0) != cudaSuccess)
+    if (cudaEventRecord(aux->join[hi], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[hi], 0) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: stream join failed");
   } else {
     if ((rc = run_direction<NV, VW>(cost, image, T, H, W, D, p1, p2, 1, 0, H, min_limit, 0u, nullptr, -1, helper)))
@@ -814,7 +816,7 @@ static int sgm_fused_overlap(const float *cost, const float *image, float *out, 
     rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 2, ws, ws_bytes, stream);
     if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
     if (rc) return rc;
-    if (cudaEventRecord(aux->join[0], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[0], 0) != cudaSuccess)
+    if (cudaEventRecord(aux->join[hi], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[hi], 0) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: stream join failed");
   }
   pass_mark(1, 3, stream);

@@ -49,8 +49,20 @@ class Pipeline:
         # `_aggregation_volume` after estimate().
         self.keep_aggregation_volume = False
 
-    def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor) -> torch.Tensor:
-        """[H,W] left/right images (CUDA float32) -> int32 [H,W] disparity map."""
+    def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """[H,W] left/right images (CUDA float32) -> int32 [H,W] disparity map.
+
+        out (new, optional): an int32 [H,W] tensor on the images' device that receives the map
+        instead of the pipeline's own reused buffer (callers that keep several frames in flight,
+        stereomatch.streaming); it is not retained."""
+        if out is not None:
+            keep = self._disparity_image
+            self._disparity_image = out
+            try:
+                return self.estimate(left_image, right_image)
+            finally:
+                self._disparity_image = keep
         if (self.fuse_cost_and_reduce and self.aggregation is None and type(self.cost) is Birchfield
                 and type(self.disparity_reduce) is WinnerTakesAll):
             # cost + reduce in one kernel, the volume never materialised (stm_birchfield_wta_f32)

@@ -61,12 +61,10 @@ class BatchEstimator:
             for k, (left, right) in enumerate(pairs):
                 pipe, stream = self.pipelines[k % n], self._streams[k % n]
                 with torch.cuda.stream(stream):
-                    # the pipeline writes into whatever `_disparity_image` holds: hand it the
-                    # caller's tensor (or a new one) so frames k and k+n do not share a buffer
-                    pipe._disparity_image = outs[k] if outs is not None else torch.empty(
+                    # frames k and k+n must not share a result buffer: the caller's tensor or a new one
+                    out = outs[k] if outs is not None else torch.empty(
                         tuple(left.shape), dtype=torch.int32, device=self.device)
-                    results.append(pipe.estimate(left, right))
-                    pipe._disparity_image = None
+                    results.append(pipe.estimate(left, right, out=out))
             for s in self._streams:
                 done = torch.cuda.Event()
                 done.record(s)
@@ -138,9 +136,7 @@ class HostFrameStreamer:
                     cstream.wait_event(uploaded)
                     if res_free[s] is not None:
                         cstream.wait_event(res_free[s])
-                    pipe._disparity_image = self._res[s]   # written in place, no copy
-                    pipe.estimate(dl, dr)
-                    pipe._disparity_image = None
+                    pipe.estimate(dl, dr, out=self._res[s])   # written in place, no copy
                     in_free[s] = torch.cuda.Event()
                     in_free[s].record(cstream)
                     computed = in_free[s]
