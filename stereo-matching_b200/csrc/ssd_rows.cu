@@ -140,7 +140,7 @@ __device__ __forceinline__ void ssd_rows_item(const float2 *rb, float *hb, int i
 template <int K, int RUNS, int NH>
 __global__ void __launch_bounds__(ssdr::Cfg<K, RUNS, NH>::THREADS, 1)
 ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right, float *__restrict__ cost,
-                int H, int W, int D, int rows_per_chunk, int d_fastest, int store_policy) {
+                int H, int W, int D, int rows_per_chunk, int d_fastest) {
   using namespace ssdr;
   using C = Cfg<K, RUNS, NH>;
   constexpr int WIN = C::WIN, PAIRS = C::PAIRS, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
@@ -237,10 +237,8 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
           if (y >= ya && y < yb) {  // block-uniform
             float *o = ocol + (size_t)y * W * D;
             if (plain) {
-              const float4 o4 = make_float4(out[0], out[1], out[2], out[3]);
-              if (store_policy == 0) __stcs(reinterpret_cast<float4 *>(o), o4);
-              else if (store_policy == 1) *reinterpret_cast<float4 *>(o) = o4;
-              else __stwt(reinterpret_cast<float4 *>(o), o4);
+              // streaming (evict-first) store: plain and write-through stores measured 0.43 vs 0.385 ms
+              __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
             } else {
 #pragma unroll
               for (int j = 0; j < 4; ++j)
@@ -315,10 +313,7 @@ static int run_ssd_rows(const float *left, const float *right, float *cost, int 
   const int d_fastest = !(order && order[0] == 'x');
   if (nx > 65535) return fail(STM_EUNSUPPORTED, "ssd: shape too large");
   const dim3 grid = d_fastest ? dim3(nd, nx, ny) : dim3(nx, nd, ny);
-  static const char *pol = getenv("STM_DEBUG_SSD_STORE");  // developer knob: 0 = .cs (default), 1 = plain, 2 = .wt
-  const int store_policy = pol ? atoi(pol) : 0;
-  ssd_rows_kernel<K, RUNS, NH><<<grid, C::THREADS, C::SMEM, stream>>>(left, right, cost, H, W, D, rows, d_fastest,
-                                                                        store_policy);
+  ssd_rows_kernel<K, RUNS, NH><<<grid, C::THREADS, C::SMEM, stream>>>(left, right, cost, H, W, D, rows, d_fastest);
   return check_launch("ssd_rows_kernel");
 }
 
