@@ -224,8 +224,8 @@ __device__ __forceinline__ void lv_argmin_store(const LaneVec<NV, VW> &o, int la
       if (d < D && o.v[k][j] == m) idx = (unsigned)d;  // descending d: the lowest one sticks
     }
   idx = __reduce_min_sync(FULL, idx);
-  const bool nan0 = __shfl_sync(FULL, (o.v[0][0] != o.v[0][0]) ? 1 : 0, 0) != 0;
-  if (lane == 0) *dst = (nan0 || idx == 0x7fffffffu) ? 0 : (int)idx;
+  // NaN at d = 0 -> 0: d = 0 is element (0, 0) of lane 0, the lane that stores: no broadcast needed
+  if (lane == 0) *dst = (o.v[0][0] != o.v[0][0] || idx == 0x7fffffffu) ? 0 : (int)idx;
 }
 
 }  // namespace stm

@@ -578,11 +578,12 @@ static int sgm_by_direction_portrait(const float *cost, const float *image, floa
 
 // sgm_vsweep.cu
 size_t sgm_vsweep_workspace_bytes(int H, int W, int D);
-bool sgm_vsweep_can_run(int H, int W, int D, bool three_streams);
+bool sgm_vsweep_can_run(int H, int W, int D, int variant_group);  // 0: the plain pair; 1: + overwrite / 3 streams; 2: + 4 streams
 int launch_sgm_vsweep_prepare(const float *, int, int, int, float, float, void *, cudaStream_t);
-int launch_sgm_vsweep(const float *cost, const float *image, float *out, const float *extra, int32_t *disp,
-                      int H, int W, int D, float p1, float p2, int min_limit, int up, bool store_vol,
-                      int volume_streams, void *workspace, size_t workspace_bytes, cudaStream_t stream);
+int launch_sgm_vsweep(const float *cost, const float *image, float *out, const float *extra, const float *extra2,
+                      int32_t *disp, int H, int W, int D, float p1, float p2, int min_limit, int up,
+                      bool store_vol, int volume_streams, void *workspace, size_t workspace_bytes,
+                      cudaStream_t stream);
 
 // STM_SGM_FUSED_SWEEPS: the two horizontal directions as passes of their own, then the six
 // directions with a vertical component as two fused sweeps (sgm_vsweep.cu): four passes over
@@ -593,7 +594,7 @@ static int sgm_fused(const float *cost, const float *image, float *out, int H, i
                      float p1, float p2, unsigned flags, void *ws, size_t ws_bytes,
                      cudaStream_t stream, int32_t *disp) {
   const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
-  if (ws == nullptr || ws_bytes < sgm_vsweep_workspace_bytes(H, W, D) || !sgm_vsweep_can_run(H, W, D, false))
+  if (ws == nullptr || ws_bytes < sgm_vsweep_workspace_bytes(H, W, D) || !sgm_vsweep_can_run(H, W, D, 0))
     return 1;
   if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) |
        reinterpret_cast<uintptr_t>(ws)) & 15)
@@ -608,12 +609,12 @@ static int sgm_fused(const float *cost, const float *image, float *out, int H, i
   }
   pass_mark(2, 2, stream);
   if ((rc = launch_sgm_vsweep_prepare(image, H, W, D, p1, p2, ws, stream))) return rc;
-  rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 2, ws,
+  rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 2, ws,
                          ws_bytes, stream);
   if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
   if (rc) return rc;
   pass_mark(3, 3, stream);
-  rc = launch_sgm_vsweep(cost, image, out, nullptr, disp, H, W, D, p1, p2, min_limit, 1,
+  rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, disp, H, W, D, p1, p2, min_limit, 1,
                          !(disp && (flags & STM_SGM_DISPARITY_ONLY)), 2, ws, ws_bytes, stream);
   if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
   if (rc) return rc;
@@ -649,13 +650,16 @@ size_t sgm_workspace_bytes(int H, int W, int D) {
   return align256(base) + (size_t)8 * H * W * D * sizeof(float);
 }
 static bool sgm_overlap_shape(int H, int W, int D);
-// with STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP: one more volume after the base workspace
+static bool sgm_four_stream_shape(int D);
+// with STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP: one more volume after the base workspace, and a
+// second one with STM_SGM_DISPARITY_ONLY (the four-stream schedule, see sgm_fused_overlap)
 size_t sgm_workspace_bytes_flags(int H, int W, int D, unsigned flags) {
   const size_t plain = sgm_workspace_bytes(H, W, D);
   if ((flags & (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP)) != (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP) ||
       !sgm_overlap_shape(H, W, D))
     return plain;
-  const size_t need = align256(sgm_base_workspace_bytes(H, W, D)) + (size_t)H * W * D * sizeof(float);
+  const size_t volumes = ((flags & STM_SGM_DISPARITY_ONLY) && sgm_four_stream_shape(D)) ? 2 : 1;
+  const size_t need = align256(sgm_base_workspace_bytes(H, W, D)) + volumes * H * W * D * sizeof(float);
   return need > plain ? need : plain;
 }
 
@@ -770,6 +774,14 @@ static bool sgm_overlap_shape(int H, int W, int D) {  // pure function of the sh
   return m.NV * 32 * m.VW <= 128;
 }
 
+// The four-stream form of the schedule (disparity only, see below) pays at 128 padded disparities only:
+// measured at 1080p, D=128 2.287 -> 2.248 ms; D=64 1.95 ms against 1.60 ms for the three-stream form that
+// even stores the volume (two row kernels next to the sweep slow it down more than the 4 B/pix-disp save).
+static bool sgm_four_stream_shape(int D) {
+  const LaneMap m = pick_lane_map(D);
+  return m.NV * 32 * m.VW == 128;
+}
+
 template <int NV, int VW>
 static int sgm_fused_overlap(const float *cost, const float *image, float *out, int H, int W, int D,
                              float p1, float p2, unsigned flags, void *ws, size_t ws_bytes,
@@ -777,7 +789,7 @@ static int sgm_fused_overlap(const float *cost, const float *image, float *out, 
   const int min_limit = (flags & STM_SGM_MIN_ALL_D) ? D : D - 1;
   const size_t N = (size_t)H * W * D, off = sgm_overlap_offset(H, W, D);
   if (!sgm_overlap_shape(H, W, D) || ws == nullptr || ws_bytes < off + N * sizeof(float) ||
-      !sgm_vsweep_can_run(H, W, D, true))
+      !sgm_vsweep_can_run(H, W, D, 1))
     return 1;
   if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(ws)) & 15)
     return 1;
@@ -793,13 +805,49 @@ static int sgm_fused_overlap(const float *cost, const float *image, float *out, 
   cudaStream_t helper = aux->stream[hi];
   const unsigned mode0 = (flags & STM_SGM_OVERWRITE) ? 0u : kSgmAccumulate;
   const bool store_up = !(disp && (flags & STM_SGM_DISPARITY_ONLY));
+  // Disparity only: nothing has to end up in `out`, so <- does not have to chain through it either.
+  // With a second workspace volume U the three producers are independent and all of them only write:
+  //     stream:    down sweep  T = L2 + L4 + L6          helper a:  ->  out = [out +] L0
+  //     helper b:  <-  U = L1                            (8 + 8 + 8 B/pix-disp instead of 8 + 8 + 12)
+  //     stream:    up sweep    argmin(((out + T) + U) + L3 + L5 + L7), nothing stored (16 B)
+  // The up sweep is bound by its instruction stream, not by bandwidth, so the fourth stream it
+  // reads costs less (0.81 -> 0.85 ms) than the read-modify-write it replaces (phase one 1.51 -> 1.39 ms).
+  // Developer knob STM_DEBUG_SGM_OVERLAP=3 keeps the three-stream form.
+  const bool four = !store_up && !variant_x && !(knob && knob[0] == '3') && sgm_four_stream_shape(D) &&
+                    ws_bytes >= off + 2 * N * sizeof(float) && sgm_vsweep_can_run(H, W, D, 2);
+  if (four) {
+    float *U = T + N;
+    const int hb = (hi + 3) % 7;
+    cudaStream_t helper_b = aux->stream[hb];
+    pass_mark(0, 8, stream);
+    if (cudaEventRecord(aux->fork, stream) != cudaSuccess || cudaStreamWaitEvent(helper, aux->fork, 0) != cudaSuccess ||
+        cudaStreamWaitEvent(helper_b, aux->fork, 0) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: stream fork failed");
+    if ((rc = launch_sgm_vsweep_prepare(image, H, W, D, p1, p2, ws, stream))) return rc;
+    rc = launch_sgm_vsweep(cost, image, T, nullptr, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 1, ws, ws_bytes, stream);
+    if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
+    if (rc) return rc;
+    if ((rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 0, 0, H, min_limit, mode0, nullptr, -1, helper)))
+      return rc;
+    if ((rc = run_direction<NV, VW>(cost, image, U, H, W, D, p1, p2, 1, 0, H, min_limit, 0u, nullptr, -1, helper_b)))
+      return rc;
+    if (cudaEventRecord(aux->join[hi], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[hi], 0) != cudaSuccess ||
+        cudaEventRecord(aux->join[hb], helper_b) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[hb], 0) != cudaSuccess)
+      return fail(STM_ECUDA, "sgm: stream join failed");
+    pass_mark(1, 3, stream);
+    rc = launch_sgm_vsweep(cost, image, out, T, U, disp, H, W, D, p1, p2, min_limit, 1, false, 4, ws, ws_bytes, stream);
+    if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
+    if (rc) return rc;
+    pass_mark(2, -1, stream);
+    return STM_OK;
+  }
   pass_mark(0, 8, stream);
   if (cudaEventRecord(aux->fork, stream) != cudaSuccess || cudaStreamWaitEvent(helper, aux->fork, 0) != cudaSuccess)
     return fail(STM_ECUDA, "sgm: stream fork failed");
   if ((rc = launch_sgm_vsweep_prepare(image, H, W, D, p1, p2, ws, stream))) return rc;
   if (!variant_x) {
     // the cooperative sweep first: it needs a slot on every SM; the row CTAs then fill what is left
-    rc = launch_sgm_vsweep(cost, image, T, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 1, ws, ws_bytes, stream);
+    rc = launch_sgm_vsweep(cost, image, T, nullptr, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 1, ws, ws_bytes, stream);
     if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
     if (rc) return rc;
     if ((rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 0, 0, H, min_limit, mode0, nullptr, -1, helper)))
@@ -813,14 +861,14 @@ static int sgm_fused_overlap(const float *cost, const float *image, float *out, 
       return rc;
     if ((rc = run_direction<NV, VW>(cost, image, out, H, W, D, p1, p2, 0, 0, H, min_limit, mode0, nullptr, -1, stream)))
       return rc;
-    rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 2, ws, ws_bytes, stream);
+    rc = launch_sgm_vsweep(cost, image, out, nullptr, nullptr, nullptr, H, W, D, p1, p2, min_limit, 0, true, 2, ws, ws_bytes, stream);
     if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
     if (rc) return rc;
     if (cudaEventRecord(aux->join[hi], helper) != cudaSuccess || cudaStreamWaitEvent(stream, aux->join[hi], 0) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: stream join failed");
   }
   pass_mark(1, 3, stream);
-  rc = launch_sgm_vsweep(cost, image, out, T, disp, H, W, D, p1, p2, min_limit, 1, store_up, 3, ws, ws_bytes, stream);
+  rc = launch_sgm_vsweep(cost, image, out, T, nullptr, disp, H, W, D, p1, p2, min_limit, 1, store_up, 3, ws, ws_bytes, stream);
   if (rc == 1) return fail(STM_EUNSUPPORTED, "sgm: fused sweeps refused a shape they accepted");
   if (rc) return rc;
   pass_mark(2, -1, stream);

@@ -97,7 +97,7 @@ constexpr bool kDebug = false;
 // NS = volume vectors prefetched per pixel: 1 = cost only (the sweep OVERWRITES `out` with its three
 // directions: no sum is read), 2 = cost + sum (read-modify-write of `out`), 3 = cost + sum + one more
 // volume `extra` that is added too (the other sweep's result, when the two sweeps did not chain
-// through `out`; see sgm.cu, STM_SGM_OVERLAP).
+// through `out`; see sgm.cu, STM_SGM_OVERLAP), 4 = and a second one, `extra2` (the <- pass's own volume).
 template <int DPAD, int NS = 2>
 struct Cfg {
   static constexpr int PF = (DPAD <= 128 || (DPAD <= 192 && NS <= 2)) ? kPfSmall : 4;  // prefetch ring entries per slot
@@ -115,7 +115,8 @@ struct Params {
   const float *cost;
   const float4 *pen;          // [H][W] adaptive penalties (A, B, C, -) of this sweep, see sgm_vsweep_penalties
   float *out;
-  const float *extra;         // NS == 3: a second sum volume that is added (read only)
+  const float *extra;         // NS >= 3: a second sum volume that is added (read only)
+  const float *extra2;        // NS == 4: a third one
   int32_t *disp;
   unsigned long long *xring;  // [G][kRX][3][DPAD] (value, tag) words
   unsigned *xcons;            // [G][kFlagStride] rows imported so far by CTA c (one 128-byte line each)
@@ -454,6 +455,31 @@ __device__ __forceinline__ void add_weighted(LaneVec<NV, VW> &o, const LaneVec<N
   }
 }
 
+// o += w * L for the defective up-diagonals, w in {0, 1, W-H+1} warp-uniform: w = 0 must leave o alone
+// even where L is +inf (0 * inf), hence the select; fma(1, L, o) is o + L with one rounding, exactly the
+// packed addition, and fma(w, L, o) is what the branchy version computed for the corner diagonal.
+template <int NV, int VW>
+__device__ __forceinline__ void add_scaled(LaneVec<NV, VW> &o, const LaneVec<NV, VW> &L, float w) {
+  const bool skip = w == 0.f;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    if constexpr (VW % 2 == 0) {
+#pragma unroll
+      for (int j = 0; j < VW; j += 2) {  // fma.rn.f32x2: the rounding of two FFMAs
+        unsigned long long a, b, c, d;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(w), "f"(w));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(skip ? 0.f : L.v[k][j]), "f"(skip ? 0.f : L.v[k][j + 1]));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(o.v[k][j]), "f"(o.v[k][j + 1]));
+        asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(o.v[k][j]), "=f"(o.v[k][j + 1]) : "l"(d));
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < VW; ++j) o.v[k][j] = __fmaf_rn(w, skip ? 0.f : L.v[k][j], o.v[k][j]);
+    }
+  }
+}
+
 template <int NV, int VW, bool UP, bool WTA, int NS>
 __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int base, int j, int lane) {
   constexpr int DPAD = NV * 32 * VW;
@@ -476,7 +502,8 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   // fetch side: row pointers (lane offset included) + column
   const float *crow = P.cost + (long long)y * W * D + lane_off;
   const float *srow = P.out + (long long)y * W * D + lane_off;
-  const float *xrow = (NS == 3 ? P.extra : P.out) + (long long)y * W * D + lane_off;
+  const float *xrow = (NS >= 3 ? P.extra : P.out) + (long long)y * W * D + lane_off;
+  const float *zrow = (NS == 4 ? P.extra2 : P.out) + (long long)y * W * D + lane_off;
   const float4 *prow = P.pen + (long long)y * W;
   const long long rowstep_d = rowstep * D;
   int fx = x, ft = 0;
@@ -484,7 +511,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   // row ft: cost, sum and penalties into ring entry `e`; always exactly one commit group.
   // Past the last row the last row is fetched again (never used).
   auto issue = [&](int e) {
-    const float *cs = crow + fx * D, *ss = srow + fx * D, *xs = xrow + fx * D;
+    const float *cs = crow + fx * D, *ss = srow + fx * D, *xs = xrow + fx * D, *zs = zrow + fx * D;
     float *dc = pf + e * NS * DPAD;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
@@ -492,14 +519,15 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       if ((VW > 1 || off + lane < D) && !(kDebug && (P.dbg & 32))) {
         cp_async<VW * 4>(dc + off, cs + off);
         if constexpr (NS >= 2) cp_async<VW * 4>(dc + DPAD + off, ss + off);
-        if constexpr (NS == 3) cp_async<VW * 4>(dc + 2 * DPAD + off, xs + off);
+        if constexpr (NS >= 3) cp_async<VW * 4>(dc + 2 * DPAD + off, xs + off);
+        if constexpr (NS == 4) cp_async<VW * 4>(dc + 3 * DPAD + off, zs + off);
       }
     }
     if (lane == 0) cp_async<16>(reinterpret_cast<float *>(pfi + e), reinterpret_cast<const float *>(prow + fx));
     cp_async_commit();
     if (ft + 1 < H) {
       ++ft;
-      prow += rowstep; crow += rowstep_d; srow += rowstep_d; xrow += rowstep_d;
+      prow += rowstep; crow += rowstep_d; srow += rowstep_d; xrow += rowstep_d; zrow += rowstep_d;
       fx = fx + 1 == W ? 0 : fx + 1;
     }
   };
@@ -516,8 +544,10 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   constexpr bool emit_wta = WTA;
   int e = 0;
 
-  // penalties of the row about to be processed, computed one row ahead (off the hand-off path)
+  // penalties of the row about to be processed, computed one row ahead (off the hand-off path);
+  // pw: the up-diagonal multiplicities of that row's pixel, (mult5 << 16) | mult7 (first row: closed form)
   float pa = 0.f, pb = 0.f, pc = 0.f;
+  unsigned pw = UP ? (((unsigned)sgm_mult5(x, y, H, W) << 16) | (unsigned)sgm_mult7(x, y, H, W)) : 0u;
 
   const bool trace = kDebug && (P.dbg & 16) && blockIdx.x == kTraceCta && lane == 0;
   auto mark = [&](int t, int ev) {
@@ -541,15 +571,18 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
 #pragma unroll
         for (int q = 0; q < VW; ++q) o.v[k][q] = 0.f;  // this sweep starts the sum (0 + L is exact)
     }
-    if constexpr (NS == 3) {
-      LaneVec<NV, VW> x2;
-      lv_lds<NV, VW>(x2, pf + e * NS * DPAD + 2 * DPAD, 0);
-      if constexpr (VW == 1) {
+    if constexpr (NS >= 3) {
 #pragma unroll
-        for (int k = 0; k < NV; ++k)
-          if (k * 32 + lane >= D) x2.v[k][0] = 0.f;
+      for (int extra_i = 2; extra_i < NS; ++extra_i) {
+        LaneVec<NV, VW> x2;
+        lv_lds<NV, VW>(x2, pf + e * NS * DPAD + extra_i * DPAD, 0);
+        if constexpr (VW == 1) {
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+            if (k * 32 + lane >= D) x2.v[k][0] = 0.f;
+        }
+        add_weighted<NV, VW>(o, x2, 1);
       }
-      add_weighted<NV, VW>(o, x2, 1);
     }
     if constexpr (VW == 1) {
 #pragma unroll
@@ -623,6 +656,8 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
     asm volatile("" ::: "memory");
     issue(e_refill);
     pa = pn.x; pb = pn.y; pc = pn.z;
+    const unsigned w_now = pw;
+    pw = __float_as_uint(pn.w);
 
     // sum in the reference's direction order: down 2, 4, 6 = B, A, C; up 3, 5, 7 = B, C, A
     add_weighted<NV, VW>(o, LB, 1);
@@ -633,8 +668,8 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       add_weighted<NV, VW>(o, LC, 1);
       add_weighted<NV, VW>(o, LA, 1);
     } else {
-      add_weighted<NV, VW>(o, LC, sgm_mult5(x, y, H, W));
-      add_weighted<NV, VW>(o, LA, sgm_mult7(x, y, H, W));
+      add_scaled<NV, VW>(o, LC, (float)(w_now >> 16));
+      add_scaled<NV, VW>(o, LA, (float)(w_now & 0xffffu));
     }
     if (store_vol && !(kDebug && (P.dbg & 32))) lv_store<NV, VW, true>(o, orow + x * D, 0, D - lane_off);
     if (emit_wta) lv_argmin_store<NV, VW>(o, lane, D, drow + x);
@@ -700,6 +735,10 @@ __global__ void sgm_vsweep_penalties(const float *__restrict__ image, float4 *__
       r.y = sgm_p2_adjusted(p1, p2, v, q[x]);
       r.z = sgm_p2_adjusted(p1, p2, v, q[xr]);
     }
+    // up sweep: how often the reference runs the up-diagonals through this pixel (0, 1 or W-H+1,
+    // SURVEY.md F5), packed as (mult5 << 16) | mult7 -- both <= 32767 -- so that the sweep does
+    // not evaluate the closed forms per pixel
+    if (up) r.w = __uint_as_float(((unsigned)sgm_mult5(x, y, H, W) << 16) | (unsigned)sgm_mult7(x, y, H, W));
     pen[(size_t)up * H * W + i] = r;
   }
 }
@@ -724,6 +763,7 @@ static const void *variant(size_t *smem_bytes) {
 template <int NV, int VW>
 static const void *sweep_kernel(bool up, bool wta, int ns, size_t *smem_bytes) {
   if (!up) return ns == 1 ? variant<NV, VW, false, false, 1>(smem_bytes) : variant<NV, VW, false, false, 2>(smem_bytes);
+  if (ns == 4) return wta ? variant<NV, VW, true, true, 4>(smem_bytes) : nullptr;  // Pipeline path only
   if (ns == 3) return wta ? variant<NV, VW, true, true, 3>(smem_bytes) : variant<NV, VW, true, false, 3>(smem_bytes);
   return wta ? variant<NV, VW, true, true, 2>(smem_bytes) : variant<NV, VW, true, false, 2>(smem_bytes);
 }
@@ -731,17 +771,19 @@ static const void *sweep_kernel(bool up, bool wta, int ns, size_t *smem_bytes) {
 // CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.  `ns3`: the caller
 // wants the three-stream up sweep (and the overwriting down sweep) as well.
 template <int NV, int VW>
-static int ctas(int W, bool ns3) {
-  static PerDeviceInt cache[2];  // per instantiation and device (attribute opt-in + occupancy)
+static int ctas(int W, int group) {  // group 0: NS = 2 only; 1: + NS 1 and 3; 2: + NS 4
+  const bool ns3 = group >= 1;
+  static PerDeviceInt cache[3];  // per instantiation and device (attribute opt-in + occupancy)
   const int dev = device_slot();
   int cap = 0;
-  if (!cache[ns3 ? 1 : 0].get(dev, &cap)) {
+  if (!cache[group].get(dev, &cap)) {
     int per_sm = 1 << 30;
-    for (int v = 0; v < 6; ++v) {
-      const int ns = v < 3 ? 2 : (v == 3 ? 1 : 3);
+    for (int v = 0; v < 7; ++v) {
+      const int ns = v < 3 ? 2 : (v == 3 ? 1 : (v == 6 ? 4 : 3));
       if (!ns3 && ns != 2) continue;
+      if (ns == 4 && group < 2) continue;
       size_t bytes = 0;
-      const void *k = sweep_kernel<NV, VW>(v != 0 && v != 3, v == 2 || v == 5, ns, &bytes);
+      const void *k = sweep_kernel<NV, VW>(v != 0 && v != 3, v == 2 || v == 5 || v == 6, ns, &bytes);
       int n = 0;
       if (k == nullptr) { per_sm = 0; break; }
       if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess ||
@@ -753,7 +795,7 @@ static int ctas(int W, bool ns3) {
     }
     per_sm = per_sm > 1 ? 1 : per_sm;  // one CTA per SM: the ring is sized for it
     cap = per_sm * num_sms();
-    cache[ns3 ? 1 : 0].set(dev, cap);
+    cache[group].set(dev, cap);
   }
   int G = cap < kMaxCtas ? cap : kMaxCtas;
   if (G > W / 2) G = W / 2;
@@ -762,16 +804,16 @@ static int ctas(int W, bool ns3) {
 }
 
 template <int NV, int VW>
-static int run(const float *cost, const float *image, float *out, const float *extra, int32_t *disp, int H,
-               int W, int D, float p1, float p2, int min_limit, int up, bool store_vol, int ns, char *ws,
-               cudaStream_t stream) {
+static int run(const float *cost, const float *image, float *out, const float *extra, const float *extra2,
+               int32_t *disp, int H, int W, int D, float p1, float p2, int min_limit, int up, bool store_vol,
+               int ns, char *ws, cudaStream_t stream) {
   constexpr int DPAD = NV * 32 * VW;
   size_t smem_bytes = 0;
   const void *kernel = sweep_kernel<NV, VW>(up != 0, disp != nullptr, ns, &smem_bytes);
-  const int G = ctas<NV, VW>(W, ns != 2);
+  const int G = ctas<NV, VW>(W, ns == 2 ? 0 : (ns == 4 ? 2 : 1));
   if (G < 1 || kernel == nullptr) return 1;
   Params P;
-  P.cost = cost; P.out = out; P.extra = extra; P.disp = disp;
+  P.cost = cost; P.out = out; P.extra = extra; P.extra2 = extra2; P.disp = disp;
   P.pen = reinterpret_cast<const float4 *>(ws + flags_and_rings_bytes(DPAD)) + (up ? (size_t)H * W : 0);
   P.xcons = reinterpret_cast<unsigned *>(ws);
   P.xring = reinterpret_cast<unsigned long long *>(ws + align256(kMaxCtas * kFlagStride * sizeof(unsigned)));
@@ -826,11 +868,11 @@ int launch_sgm_vsweep_prepare(const float *image, int H, int W, int D, float p1,
 }
 
 // Whether launch_sgm_vsweep will take this shape on the current device.
-bool sgm_vsweep_can_run(int H, int W, int D, bool three_streams) {
+bool sgm_vsweep_can_run(int H, int W, int D, int variant_group) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return false;
   const LaneMap m = pick_lane_map(D);
 #define STM_VSWEEP_CASE(NV_, VW_) \
-  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W, three_streams) > 0;
+  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W, variant_group) > 0;
   STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
   STM_VSWEEP_CASE(1, 1)
 #undef STM_VSWEEP_CASE
@@ -840,20 +882,24 @@ bool sgm_vsweep_can_run(int H, int W, int D, bool three_streams) {
 // One fused sweep: out += L2+L4+L6 (up = 0) or L3+L5+L7 (up = 1, reference multiplicities),
 // optionally without writing the sums back (store_vol = false) and/or emitting the disparity
 // map.  Returns 1 when the shape is not handled here (the caller runs the directions one by one).
-int launch_sgm_vsweep(const float *cost, const float *image, float *out, const float *extra, int32_t *disp,
-                      int H, int W, int D, float p1, float p2, int min_limit, int up, bool store_vol,
-                      int volume_streams, void *workspace, size_t workspace_bytes, cudaStream_t stream) {
+int launch_sgm_vsweep(const float *cost, const float *image, float *out, const float *extra, const float *extra2,
+                      int32_t *disp, int H, int W, int D, float p1, float p2, int min_limit, int up,
+                      bool store_vol, int volume_streams, void *workspace, size_t workspace_bytes,
+                      cudaStream_t stream) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return 1;
   if (workspace == nullptr || workspace_bytes < sgm_vsweep_workspace_bytes(H, W, D)) return 1;
   if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out) |
-       reinterpret_cast<uintptr_t>(workspace) | reinterpret_cast<uintptr_t>(extra)) & 15)
+       reinterpret_cast<uintptr_t>(workspace) | reinterpret_cast<uintptr_t>(extra) |
+       reinterpret_cast<uintptr_t>(extra2)) & 15)
     return 1;
-  if (volume_streams < 1 || volume_streams > 3 || (volume_streams == 3) != (extra != nullptr)) return 1;
+  if (volume_streams < 1 || volume_streams > 4 || (volume_streams >= 3) != (extra != nullptr) ||
+      (volume_streams == 4) != (extra2 != nullptr))
+    return 1;
   const LaneMap m = pick_lane_map(D);
   char *ws = static_cast<char *>(workspace);
 #define STM_VSWEEP_CASE(NV_, VW_)      \
   if (m.NV == NV_ && m.VW == VW_)      \
-    return vsweep::run<NV_, VW_>(cost, image, out, extra, disp, H, W, D, p1, p2, min_limit, up, store_vol, \
+    return vsweep::run<NV_, VW_>(cost, image, out, extra, extra2, disp, H, W, D, p1, p2, min_limit, up, store_vol, \
                                  volume_streams, ws, stream);
   STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
   STM_VSWEEP_CASE(1, 1)

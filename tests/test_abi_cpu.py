@@ -59,6 +59,14 @@ def test_workspace_query_is_pure():
     for H, W, D, dpad in ((375, 450, 64, 64), (20, 30, 32, 32), (64, 64, 128, 128)):
         assert lib.stm_sgm_workspace_bytes(H, W, D) == a256(expect(H, W, dpad)) + 8 * H * W * D * 4
     assert lib.stm_sgm_workspace_bytes(480, 640, 128) == expect(480, 640, 128)   # 157 MB: sequential
+    # the overlapped schedule (STM_SGM_FUSED_SWEEPS 4 | STM_SGM_OVERLAP 32): one more volume after the
+    # base workspace, two with STM_SGM_DISPARITY_ONLY (8) at 128 padded disparities; none at D > 128
+    lib.stm_sgm_workspace_bytes_flags.restype = ctypes.c_size_t
+    H, W = 1080, 1920
+    for D, dpad, flags, volumes in ((128, 128, 36, 1), (128, 128, 44, 2), (64, 64, 44, 1),
+                                    (192, 192, 44, 0), (128, 128, 4, 0), (128, 128, 32, 0)):
+        want = expect(H, W, dpad) if volumes == 0 else a256(expect(H, W, dpad)) + volumes * H * W * D * 4
+        assert lib.stm_sgm_workspace_bytes_flags(H, W, D, flags) == want, (D, flags)
 
 
 def test_python_api_surface_matches_reference():

@@ -45,6 +45,8 @@ for name, ov in (("plain", False), ("overlap", True)):
     AggregationOps.pass_timing(True)
     sgm(cost, l, vol); sgm(cost, l, vol)
     res[name + "_passes"] = [(d, round(t, 4)) for d, t in AggregationOps.last_pass_ms()]
+    sgm.aggregate_and_reduce(cost, l, vol, disp, keep_volume=False); sgm.aggregate_and_reduce(cost, l, vol, disp, keep_volume=False)
+    res[name + "_disparity_only_passes"] = [(d, round(t, 4)) for d, t in AggregationOps.last_pass_ms()]
     AggregationOps.pass_timing(False)
 res["maps_differ"] = float((maps["plain"] != maps["overlap"]).float().mean())
 print(json.dumps(res))
