@@ -65,7 +65,7 @@ constexpr int kPfSmall = STM_VSWEEP_PF;
 constexpr int kImporterLook = STM_VSWEEP_LOOK;  // 1: measured, see importer_core
 constexpr int kLookMax = 4;       // rows of that ring the importer keeps loads in flight for
 constexpr int kFlagStride = 32;  // unsigned per counter: counters of different CTAs never share a line
-constexpr int kMaxCtas = 192;  // workspace is sized for this many (pure function of the shape)
+constexpr int kMaxCtas = 320;  // workspace is sized for this many (pure function of the shape): two per SM on 160 SMs
 constexpr int kThreads = (kCols + 2) * 32;  // column slots + importer + exporter
 constexpr int kExporterBox = kCols + 1;      // barrier index of the exporter's inbox (never a consumer slot)
 // A polling loop that makes no progress for kSpinSeconds of wall clock traps instead of hanging
@@ -690,8 +690,10 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
   }
 }
 
-template <int NV, int VW, bool UP, bool WTA, int NS>
-__global__ void __launch_bounds__(kThreads, 1) sgm_vsweep_kernel(const Params P) {
+// MINB = 2: the same kernel compiled for two CTAs per SM (64 registers), for images wider than
+// kCols columns per SM; only for the lane maps with at most two disparities per lane (D <= 64).
+template <int NV, int VW, bool UP, bool WTA, int NS, int MINB = 1>
+__global__ void __launch_bounds__(kThreads, MINB) sgm_vsweep_kernel(const Params P) {
   extern __shared__ __align__(128) unsigned char smem[];
   using C = Cfg<NV * 32 * VW, NS>;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -750,10 +752,16 @@ static size_t flags_and_rings_bytes(size_t dpad) {
 // The six variants of one lane map: (up?, argmin?, volume streams).  nullptr = does not fit in
 // shared memory for this lane map (three streams at D = 256).
 template <int NV, int VW, bool UP, bool WTA, int NS>
-static const void *variant(size_t *smem_bytes) {
+static const void *variant(size_t *smem_bytes, int minb = 1) {
   using C = Cfg<NV * 32 * VW, NS>;
   if constexpr (C::kFits) {
     *smem_bytes = (size_t)C::kBytes;
+    if (minb == 2) {
+      if constexpr (NV * VW <= 2 && 2 * C::kBytes + 2048 <= 227 * 1024)
+        return (const void *)sgm_vsweep_kernel<NV, VW, UP, WTA, NS, 2>;
+      else
+        return nullptr;
+    }
     return (const void *)sgm_vsweep_kernel<NV, VW, UP, WTA, NS>;
   } else {
     *smem_bytes = 0;
@@ -761,46 +769,55 @@ static const void *variant(size_t *smem_bytes) {
   }
 }
 template <int NV, int VW>
-static const void *sweep_kernel(bool up, bool wta, int ns, size_t *smem_bytes) {
-  if (!up) return ns == 1 ? variant<NV, VW, false, false, 1>(smem_bytes) : variant<NV, VW, false, false, 2>(smem_bytes);
-  if (ns == 4) return wta ? variant<NV, VW, true, true, 4>(smem_bytes) : nullptr;  // Pipeline path only
-  if (ns == 3) return wta ? variant<NV, VW, true, true, 3>(smem_bytes) : variant<NV, VW, true, false, 3>(smem_bytes);
-  return wta ? variant<NV, VW, true, true, 2>(smem_bytes) : variant<NV, VW, true, false, 2>(smem_bytes);
+static const void *sweep_kernel(bool up, bool wta, int ns, size_t *smem_bytes, int minb = 1) {
+  size_t *b = smem_bytes;
+  if (!up) return ns == 1 ? variant<NV, VW, false, false, 1>(b, minb) : variant<NV, VW, false, false, 2>(b, minb);
+  if (ns == 4) return wta ? variant<NV, VW, true, true, 4>(b, minb) : nullptr;  // Pipeline path only
+  if (ns == 3) return wta ? variant<NV, VW, true, true, 3>(b, minb) : variant<NV, VW, true, false, 3>(b, minb);
+  return wta ? variant<NV, VW, true, true, 2>(b, minb) : variant<NV, VW, true, false, 2>(b, minb);
 }
 
-// CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.  `ns3`: the caller
-// wants the three-stream up sweep (and the overwriting down sweep) as well.
+// CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.  group 0: the plain
+// pair of sweeps (NS = 2); 1: the overwriting down sweep and the three-stream up sweep as well; 2: and
+// the four-stream one.  *minb = CTAs per SM the kernels must be compiled for: 1, or 2 when the image
+// is wider than kCols columns per SM and the lane map has a two-CTA build (D <= 64).
 template <int NV, int VW>
-static int ctas(int W, int group) {  // group 0: NS = 2 only; 1: + NS 1 and 3; 2: + NS 4
-  const bool ns3 = group >= 1;
-  static PerDeviceInt cache[3];  // per instantiation and device (attribute opt-in + occupancy)
+static int ctas(int W, int group, int *minb_out) {
+  static PerDeviceInt cache[3][2];  // per instantiation and device (attribute opt-in + occupancy)
   const int dev = device_slot();
-  int cap = 0;
-  if (!cache[group].get(dev, &cap)) {
-    int per_sm = 1 << 30;
-    for (int v = 0; v < 7; ++v) {
-      const int ns = v < 3 ? 2 : (v == 3 ? 1 : (v == 6 ? 4 : 3));
-      if (!ns3 && ns != 2) continue;
-      if (ns == 4 && group < 2) continue;
-      size_t bytes = 0;
-      const void *k = sweep_kernel<NV, VW>(v != 0 && v != 3, v == 2 || v == 5 || v == 6, ns, &bytes);
-      int n = 0;
-      if (k == nullptr) { per_sm = 0; break; }
-      if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess ||
-          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, kThreads, bytes) != cudaSuccess) {
-        cudaGetLastError();
-        return 0;
+  for (int minb = 1; minb <= 2; ++minb) {
+    int cap = 0;
+    if (!cache[group][minb - 1].get(dev, &cap)) {
+      int per_sm = 1 << 30;
+      for (int v = 0; v < 7; ++v) {
+        const int ns = v < 3 ? 2 : (v == 3 ? 1 : (v == 6 ? 4 : 3));
+        if (group < 1 && ns != 2) continue;
+        if (ns == 4 && group < 2) continue;
+        size_t bytes = 0;
+        const void *k = sweep_kernel<NV, VW>(v != 0 && v != 3, v == 2 || v == 5 || v == 6, ns, &bytes, minb);
+        int n = 0;
+        if (k == nullptr) { per_sm = 0; break; }
+        if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess ||
+            (minb == 2 && cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                               cudaSharedmemCarveoutMaxShared) != cudaSuccess) ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, kThreads, bytes) != cudaSuccess) {
+          cudaGetLastError();
+          return 0;
+        }
+        per_sm = n < per_sm ? n : per_sm;
       }
-      per_sm = n < per_sm ? n : per_sm;
+      per_sm = per_sm >= minb ? minb : 0;  // exactly minb CTAs per SM: the rings are sized for it
+      cap = per_sm * num_sms();
+      cache[group][minb - 1].set(dev, cap);
     }
-    per_sm = per_sm > 1 ? 1 : per_sm;  // one CTA per SM: the ring is sized for it
-    cap = per_sm * num_sms();
-    cache[group].set(dev, cap);
+    int G = cap < kMaxCtas ? cap : kMaxCtas;
+    if (G > W / 2) G = W / 2;
+    if (G >= 1 && (W + G - 1) / G <= kCols) {
+      *minb_out = minb;
+      return G;
+    }
   }
-  int G = cap < kMaxCtas ? cap : kMaxCtas;
-  if (G > W / 2) G = W / 2;
-  if (G < 1 || (W + G - 1) / G > kCols) return 0;
-  return G;
+  return 0;
 }
 
 template <int NV, int VW>
@@ -809,9 +826,11 @@ static int run(const float *cost, const float *image, float *out, const float *e
                int ns, char *ws, cudaStream_t stream) {
   constexpr int DPAD = NV * 32 * VW;
   size_t smem_bytes = 0;
-  const void *kernel = sweep_kernel<NV, VW>(up != 0, disp != nullptr, ns, &smem_bytes);
-  const int G = ctas<NV, VW>(W, ns == 2 ? 0 : (ns == 4 ? 2 : 1));
-  if (G < 1 || kernel == nullptr) return 1;
+  int minb = 1;
+  const int G = ctas<NV, VW>(W, ns == 2 ? 0 : (ns == 4 ? 2 : 1), &minb);
+  if (G < 1) return 1;
+  const void *kernel = sweep_kernel<NV, VW>(up != 0, disp != nullptr, ns, &smem_bytes, minb);
+  if (kernel == nullptr) return 1;
   Params P;
   P.cost = cost; P.out = out; P.extra = extra; P.extra2 = extra2; P.disp = disp;
   P.pen = reinterpret_cast<const float4 *>(ws + flags_and_rings_bytes(DPAD)) + (up ? (size_t)H * W : 0);
@@ -871,8 +890,9 @@ int launch_sgm_vsweep_prepare(const float *image, int H, int W, int D, float p1,
 bool sgm_vsweep_can_run(int H, int W, int D, int variant_group) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return false;
   const LaneMap m = pick_lane_map(D);
+  int minb = 1;
 #define STM_VSWEEP_CASE(NV_, VW_) \
-  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W, variant_group) > 0;
+  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W, variant_group, &minb) > 0;
   STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
   STM_VSWEEP_CASE(1, 1)
 #undef STM_VSWEEP_CASE

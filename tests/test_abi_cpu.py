@@ -42,11 +42,11 @@ def test_workspace_query_is_pure():
 
     def expect(H, W, dpad):
         # max of csrc/sgm.cu (one path's vectors for the corner-diagonal replay) and
-        # csrc/sgm_vsweep.cu (192 imported-row counters of 128 B + 192 CTA->CTA rings of
+        # csrc/sgm_vsweep.cu (320 imported-row counters of 128 B + 320 CTA->CTA rings of
         # 16 rows x 3 vectors of 8-byte (value, tag) words; only for the lane maps it handles)
         direction = min(H, W) * dpad * 4
         # + the adaptive penalties of both sweeps, one float4 per pixel each
-        sweeps = (24576 + 192 * 16 * 3 * dpad * 8 + 2 * H * W * 16
+        sweeps = (40960 + 320 * 16 * 3 * dpad * 8 + 2 * H * W * 16
                   if (H >= 2 and W >= 2 and dpad in (32, 64, 128, 192, 256)) else 0)
         return max(direction, sweeps)
 

@@ -240,3 +240,41 @@ def test_1080p_d192_frame_of_the_video_batch_vs_oracle(sm, seed):
     assert m <= MAX_MISMATCH
     valid = np.arange(W)[None, :] >= gt + 7
     assert (owta[valid] == gt[valid]).mean() > 0.99
+
+
+# ------------------------------------------------- beyond the named shapes: 3840 x 2160, D = 64
+def test_4k_d64_two_sweep_ctas_per_sm_vs_oracle(sm):
+    """3840 columns are more than 13 column slots x 148 SMs: the fused sweeps run their two-CTAs-
+    per-SM build (64 registers, lane maps with <= 2 disparities per lane; csrc/sgm_vsweep.cu) instead
+    of falling back to eight direction passes.  Same bars as the named shapes; the number of passes
+    the library timed says which schedule ran."""
+    from stereomatch._cstereomatch import AggregationOps
+    H, W, D = 2160, 3840, 64
+    left, right, gt = synth.random_dot_pair(H, W, D, seed=4000, scale="raw")
+    l, r = cuda(left), cuda(right)
+    ocost = O.ssd_exact_int(left, right, D, 7)
+    cost = sm.cost.SSD(D)(l, r)
+    volume_close(cost, ocost, exact=True)
+    oagg = O.sgm(ocost, left, 0.1, 0.2)
+    owta = O.wta(oagg)
+    del ocost
+    default = sm.aggregation.Semiglobal(0.1, 0.2)
+    assert default._use_fused_sweeps(cost)
+    AggregationOps.pass_timing(True)
+    agg = default(cost, l)
+    passes = AggregationOps.last_pass_ms()
+    plain = sm.aggregation.Semiglobal(0.1, 0.2, overlap=False)
+    agg_plain = plain(cost, l)
+    passes_plain = AggregationOps.last_pass_ms()
+    AggregationOps.pass_timing(False)
+    assert len(passes) == 2 and len(passes_plain) == 4, (passes, passes_plain)   # not the 8 direction passes
+    err = volume_close(agg, oagg)
+    err_plain = volume_close(agg_plain, oagg)
+    del oagg, agg, agg_plain
+    pipe = sm.Pipeline(sm.cost.SSD(D), sm.disparity_reduce.WinnerTakesAll(), sm.aggregation.Semiglobal(0.1, 0.2))
+    m = mismatch(pipe.estimate(l, r), owta)
+    print(f"4K D=64: sums max rel err {err:.2e} (overlapped) {err_plain:.2e} (plain fused), Pipeline map "
+          f"mismatch {m:.2e}; passes ms {[round(t, 3) for _, t in passes]} / {[round(t, 3) for _, t in passes_plain]}")
+    assert m <= MAX_MISMATCH
+    valid = np.arange(W)[None, :] >= gt + 7
+    assert (owta[valid] == gt[valid]).mean() > 0.99

@@ -156,12 +156,14 @@ def test_sgm_horizontal_bulk_copy_kernel_tiles(sm, H, W, D):
 
 @pytest.mark.parametrize("H,W,D", [(70, 150, 128), (150, 70, 64), (45, 333, 192), (33, 100, 32),
                                      (64, 64, 128), (5, 700, 64), (130, 9, 16), (24, 1900, 64),
-                                     (40, 1920, 128), (37, 301, 256), (3, 2, 32), (2, 5, 64)])
+                                     (40, 1920, 128), (37, 301, 256), (3, 2, 32), (2, 5, 64),
+                                     (20, 3840, 64), (9, 2500, 32), (7, 3848, 48), (6, 3850, 64)])
 def test_sgm_sweeps_many_ctas_and_ring_wraps(sm, H, W, D):
     """Fused vertical sweeps (csrc/sgm_vsweep.cu): one CTA to 148 CTAs, 2 to 13 column slots
     per CTA, more rows than every hand-off ring (4 rows in shared memory, 16 in global memory),
     slots that wrap around the image edge, landscape (defective up-diagonals),
-    portrait and square."""
+    portrait and square; widths above 13 columns per SM (two sweep CTAs per SM at D <= 64; 3850 is
+    one column too many for 296 CTAs and runs the direction passes)."""
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H + 3 * W, scale="unit")
     cost = O.ssd(left, right, D, 3)
     want = O.sgm(cost, left, 0.1, 0.2)
