@@ -179,6 +179,18 @@ int stm_sgm_static_f32(const float *cost, const float *left, float *out, int H, 
 int stm_sgm_pass_timing(int enable);
 int stm_sgm_last_pass_ms(float *ms, int *directions, int capacity);
 
+/* New; no counterpart in the reference (whose kernels cannot wait for each other).  The fused sweeps
+ * (STM_SGM_FUSED_SWEEPS) are CTAs that hand vectors to each other; a polling loop that sees no
+ * progress for 60 s gives up COOPERATIVELY -- every CTA of that launch leaves, the kernel ends, the
+ * CUDA context stays usable -- and the call's output is unspecified.  Calls are asynchronous, so the
+ * host learns of it here: returns 1 if a sweep on the current device has given up since the last
+ * call of this function (info3, if not NULL, gets {CTA, image row step, 0 = importer waiting for
+ * its neighbour / 1 = exporter waiting for credit}) and clears the record, 0 if none, < 0 on error.
+ * Meaningful after the stream has been synchronised.  The next fused-sweep call on the device also
+ * fails with STM_ECUDA and the record in stm_last_error() if nobody has collected it.  It cannot
+ * happen unless a CTA stops (a fault); it replaces round 1's __trap(). */
+int stm_sgm_sweep_aborted(unsigned *info3);
+
 /* Replaces DisparityReduceOps.run_winners_take_all(cost, disparity)
  * (reference src/disparity_reduce.cpp:6-9 -> RunWinnersTakeAll, src/winners_take_all.cu:89-114).
  * CPU rule: first (lowest-d) minimum, all-inf -> 0, NaN never wins.  Any D >= 1. */

@@ -19,6 +19,7 @@ int launch_birchfield(const float *, const float *, float *, int, int, int, cuda
 int launch_birchfield_wta(const float *, const float *, int32_t *, int, int, int, cudaStream_t);
 size_t sgm_workspace_bytes(int, int, int);
 size_t sgm_workspace_bytes_flags(int, int, int, unsigned);
+int sgm_sweep_aborted(unsigned *);  // sgm_vsweep.cu
 int sgm_pass_timing(bool);
 int sgm_last_pass_ms(float *, int *, int);
 int launch_sgm(const float *, const float *, float *, int, int, int, float, float, unsigned, void *,
@@ -156,6 +157,12 @@ int stm_sgm_wta_f32(const float *cost, const float *left, float *out, int32_t *d
 }
 
 int stm_sgm_pass_timing(int enable) { return sgm_pass_timing(enable != 0); }
+
+int stm_sgm_sweep_aborted(unsigned *info3) {
+  const int rc = require_device();
+  if (rc) return rc;
+  return sgm_sweep_aborted(info3);
+}
 
 int stm_sgm_last_pass_ms(float *ms, int *directions, int capacity) {
   STM_REQUIRE(ms && directions, "sgm_last_pass_ms: null pointer");

@@ -44,7 +44,9 @@
 // order bit for bit leave STM_SGM_FUSED_SWEEPS off.  Measurements and the designs that were
 // tried and removed: profiles/r01_v26_fused_vertical_sweeps.md, DESIGN.md 3.4.
 #include "lanevec.cuh"
+#include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <type_traits>
 
 #include "sgm_paths.cuh"
@@ -68,26 +70,26 @@ constexpr int kFlagStride = 32;  // unsigned per counter: counters of different 
 constexpr int kMaxCtas = 320;  // workspace is sized for this many (pure function of the shape): two per SM on 160 SMs
 constexpr int kThreads = (kCols + 2) * 32;  // column slots + importer + exporter
 constexpr int kExporterBox = kCols + 1;      // barrier index of the exporter's inbox (never a consumer slot)
-// A polling loop that makes no progress for kSpinSeconds of wall clock traps instead of hanging
-// the GPU (a bug, not a slow neighbour: profilers and time-slicing can stall a CTA for a long
-// time, so the guard is on %globaltimer, looked at every 4096 polls, not on an iteration count).
+// A loop that polls GLOBAL memory (the importer on its neighbour's ring, the exporter on its credit)
+// and makes no progress for `Params::spin_ns` (60 s) of wall clock GIVES UP instead of hanging the
+// GPU (a bug, not a slow neighbour: profilers and time-slicing can stall a CTA for a long time, so
+// the guard is on %globaltimer, looked at every 4096 polls, not on an iteration count).  Giving up
+// is cooperative, not a __trap() (which would take the host application's whole CUDA context with
+// it): the warp raises an abort word in the workspace (cleared by every launch), records where it
+// was in a host-mapped status block, and from then on DRAINS -- the importer stops looking at the
+// ring and feeds its CTA whatever is there, the exporter stops waiting for credit.  Every other
+// global polling loop of the launch sees the word and drains too.  Nothing inside a CTA depends on
+// another CTA any more, the column warps (whose waits are untouched: they are the hot path) run
+// their remaining rows at full speed on garbage, and the kernel ENDS with an unspecified result
+// that the host is told about (stm_sgm_sweep_aborted; the next sweep launch on the device fails
+// with the record).
 constexpr unsigned long long kSpinSeconds = 60;
+constexpr int kAbortWord = 1;  // index into Params::xcons: a spare word of CTA 0's counter line
 __device__ __forceinline__ unsigned long long global_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-struct SpinGuard {
-  unsigned polls = 0;
-  unsigned long long t0 = 0;
-  __device__ __forceinline__ void poll() {
-    if ((++polls & 4095u) == 0) {
-      const unsigned long long now = global_ns();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > kSpinSeconds * 1000000000ull) __trap();
-    }
-  }
-};
 #ifdef STM_VSWEEP_DEBUG
 constexpr bool kDebug = true;   // STM_DEBUG_VSWEEP knobs, statistics and trace compiled in
 #else
@@ -125,6 +127,9 @@ struct Params {
   int store_vol, emit_wta, defect, min_limit;
   int dbg;  // developer knob STM_DEBUG_VSWEEP: 1 = importer does not poll, 2 = slots do not wait (wrong results)
   float p1, p2;
+  unsigned long long spin_ns;      // a polling loop without progress for this long gives up
+  volatile unsigned *host_status;  // host-mapped {gave up, CTA, row, site}, or nullptr
+  int fault_cta, fault_row;        // stm_debug_vsweep_fault: that CTA's exporter stops at that row (-1: none)
 };
 
 // Developer statistics (STM_DEBUG_VSWEEP & 8), read by stm_debug_vsweep_stats: clock64 cycles.
@@ -199,6 +204,30 @@ __device__ __forceinline__ unsigned ld_relaxed_g(const unsigned *p) {
 __device__ __forceinline__ void st_relaxed_g(unsigned *p, unsigned v) {
   asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
+// Guard of a loop that polls GLOBAL memory.  poll() is true when the loop must stop waiting: somebody
+// else has given up, or this loop has seen no progress for P.spin_ns (then it raises the abort
+// word; the first to do so also writes the host-visible record).
+// (kept inline: a __noinline__ slow part measured 3 % slower on the Pipeline path, by-value 6 %; these
+// kernels are sensitive to where cold code sits)
+struct SpinGuard {
+  unsigned polls = 0;
+  unsigned long long t0 = 0;
+  __device__ __forceinline__ bool poll(const Params &P, int site, int row) {
+    if ((++polls & 4095u) != 0) return false;
+    if (ld_relaxed_g(P.xcons + kAbortWord) != 0) return true;
+    const unsigned long long now = global_ns();
+    if (t0 == 0) { t0 = now; return false; }
+    if (now - t0 <= P.spin_ns) return false;
+    st_relaxed_g(P.xcons + kAbortWord, 1u);
+    if (P.host_status != nullptr && (threadIdx.x & 31) == 0 && atomicExch(P.xcons + kAbortWord + 1, 1u) == 0u) {
+      P.host_status[1] = blockIdx.x; P.host_status[2] = (unsigned)row; P.host_status[3] = (unsigned)site;
+      __threadfence_system();
+      P.host_status[0] = 1u;
+      __threadfence_system();
+    }
+    return true;
+  }
+};
 // The recurrence with packed additions where the lane map allows it (this kernel is bound by
 // issue slots; the per-direction kernels are not and keep lv_sgm_step).
 template <int NV, int VW>
@@ -322,6 +351,7 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
   };
 
   const bool poll = !kDebug || !(P.dbg & 1), stats = kDebug && (P.dbg & 8) != 0;
+  bool drain = false;  // the launch is giving up (SpinGuard)
   const bool tracing = kDebug && (P.dbg & 16) != 0;
   unsigned long long st_polls = 0, st_ready = 0, st_credit = 0, st_rtt = 0;
   // kLook rows of (value, tag) words in flight: the L2 round trip is longer than a row
@@ -343,9 +373,9 @@ __device__ void importer_core(const unsigned bars, float *ringB, float *ringC, u
         long long c1 = (stats || tracing) ? clock64() : 0;
         unsigned tries = 0;
         SpinGuard guard;
-        while (poll && !ready(buf[i], r)) {
+        while (poll && !drain && !ready(buf[i], r)) {
           ++tries;
-          guard.poll();
+          if (guard.poll(P, 0, r)) { drain = true; break; }  // give up: feed the CTA what is there
           const long long r0 = stats ? clock64() : 0;
           load(buf[i], r);
           if (stats) { (void)ready(buf[i], r); st_rtt += clock64() - r0; }
@@ -410,6 +440,8 @@ __device__ void exporter_warp(unsigned char *smem, const Params &P, int lane) {
   const float *ringC = reinterpret_cast<const float *>(smem + C::kRingCOff);
   unsigned long long *xdst = P.xring + (size_t)blockIdx.x * kRX * 3 * DPAD;
   unsigned xc_seen = 0;
+  bool drain = false;  // the launch is giving up (SpinGuard): no more waiting for credit
+  const int fault_row = (int)blockIdx.x == P.fault_cta ? P.fault_row : 0x7fffffff;  // stm_debug_vsweep_fault
 #pragma unroll 1
   for (int t = 0; t < nrows; ++t) {
     const int e = t & (kR - 1);
@@ -423,8 +455,9 @@ __device__ void exporter_warp(unsigned char *smem, const Params &P, int lane) {
     mbar_arrive(bar_empty(bars, 1, e));
     if (t >= kRX) {  // the previous CTA has imported row t-kRX
       const unsigned need_x = (unsigned)(t - kRX + 1);
-      for (SpinGuard guard; xc_seen < need_x; guard.poll()) xc_seen = ld_relaxed_g(xcredit);
+      for (SpinGuard guard; xc_seen < need_x && !drain; drain = guard.poll(P, 1, t)) xc_seen = ld_relaxed_g(xcredit);
     }
+    if (t >= fault_row) continue;  // injected fault: this CTA stops exporting (its neighbour starves)
     unsigned long long *ex = xdst + (size_t)(t & (kRX - 1)) * 3 * DPAD;
     lv_st_ll<NV, VW>(B0, ex, lane, (unsigned)(t + 1));
     lv_st_ll<NV, VW>(C0, ex + DPAD, lane, (unsigned)(t + 1));
@@ -707,7 +740,9 @@ __global__ void __launch_bounds__(kThreads, MINB) sgm_vsweep_kernel(const Params
     mbar_init(bar_full(bars, sl, e), 64u);                             // two inputs x every lane of their writer
     mbar_init(bar_empty(bars, sl, e), readers ? 32u * readers : 1u);   // every lane of each reader
   }
-  if (threadIdx.x == 0) *reinterpret_cast<unsigned *>(smem + C::kCreditOff) = 0u;
+  if (threadIdx.x == 0) {
+    *reinterpret_cast<unsigned *>(smem + C::kCreditOff) = 0u;
+  }
   __syncthreads();
   if (wid == kCols) importer_warp<NV, VW>(smem, P, ncols, lane);
   else if (wid == kCols + 1) exporter_warp<NV, VW>(smem, P, lane);
@@ -820,6 +855,51 @@ static int ctas(int W, int group, int *minb_out) {
   return 0;
 }
 
+// ---- give-up status (SpinGuard): one host-mapped block of four words per device ----------------
+struct SweepStatus {
+  std::mutex mu;
+  unsigned *host = nullptr;  // {gave up, CTA, row, site}; pinned and mapped, written by the kernel
+  unsigned *dev = nullptr;
+  bool tried = false;
+};
+static SweepStatus g_status[kMaxDevices];
+static int g_fault_cta = -1, g_fault_row = 0;             // stm_debug_vsweep_fault
+static unsigned long long g_spin_ns = kSpinSeconds * 1000000000ull;
+
+// The current device's block (allocated on first use; without it the kernel still gives up, but the
+// host is not told), or nullptr.
+static SweepStatus *sweep_status() {
+  const int dev = device_slot();
+  if (dev < 0) return nullptr;
+  SweepStatus &st = g_status[dev];
+  std::lock_guard<std::mutex> lock(st.mu);
+  if (!st.tried) {
+    st.tried = true;
+    void *h = nullptr, *d = nullptr;
+    if (cudaHostAlloc(&h, 64, cudaHostAllocMapped) == cudaSuccess &&
+        cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) {
+      st.host = static_cast<unsigned *>(h);
+      st.dev = static_cast<unsigned *>(d);
+      for (int i = 0; i < 16; ++i) st.host[i] = 0u;
+    } else {
+      cudaGetLastError();
+    }
+  }
+  return st.host ? &st : nullptr;
+}
+// 1 and the record (CTA, row, site) if a sweep on the current device has given up since the last
+// call; the record is cleared.
+static int take_sweep_abort(unsigned *info3) {
+  SweepStatus *st = sweep_status();
+  if (st == nullptr) return 0;
+  std::lock_guard<std::mutex> lock(st->mu);
+  volatile unsigned *h = st->host;
+  if (h[0] == 0u) return 0;
+  if (info3) { info3[0] = h[1]; info3[1] = h[2]; info3[2] = h[3]; }
+  h[0] = 0u;
+  return 1;
+}
+
 template <int NV, int VW>
 static int run(const float *cost, const float *image, float *out, const float *extra, const float *extra2,
                int32_t *disp, int H, int W, int D, float p1, float p2, int min_limit, int up, bool store_vol,
@@ -842,6 +922,20 @@ static int run(const float *cost, const float *image, float *out, const float *e
   P.min_limit = min_limit; P.p1 = p1; P.p2 = p2;
   static const char *dbg = getenv("STM_DEBUG_VSWEEP");
   P.dbg = dbg ? atoi(dbg) : 0;
+  SweepStatus *status = sweep_status();
+  P.host_status = status ? status->dev : nullptr;
+  P.spin_ns = g_spin_ns; P.fault_cta = g_fault_cta; P.fault_row = g_fault_row;
+  {
+    unsigned info[3];
+    if (take_sweep_abort(info)) {
+      char msg[200];
+      snprintf(msg, sizeof msg,
+               "sgm: a fused sweep launched earlier on this device made no progress for %.0f s and gave up "
+               "(CTA %u, row %u, %s); that call's output is invalid",
+               (double)g_spin_ns * 1e-9, info[0], info[1], info[2] ? "exporter waiting for credit" : "importer waiting for its neighbour");
+      return fail(STM_ECUDA, "%s", msg);
+    }
+  }
   // tags are row numbers: clear the counters and the rings this launch will use
   STM_CUDA_TRY(cudaMemsetAsync(ws, 0, align256(kMaxCtas * kFlagStride * sizeof(unsigned)) +
                                           (size_t)G * kRX * 3 * DPAD * sizeof(unsigned long long), stream));
@@ -851,6 +945,14 @@ static int run(const float *cost, const float *image, float *out, const float *e
 }
 
 }  // namespace vsweep
+
+// Developer hook (tests/test_gpu_sweep_abort.py): CTA `cta`'s exporter stops at row `row` (cta < 0: no
+// fault) and polling loops give up after `timeout_ms` (0: the default 60 s).  Process-wide.
+extern "C" __attribute__((visibility("default"))) int stm_debug_vsweep_fault(int cta, int row, unsigned timeout_ms) {
+  vsweep::g_fault_cta = cta; vsweep::g_fault_row = row;
+  vsweep::g_spin_ns = timeout_ms ? (unsigned long long)timeout_ms * 1000000ull : vsweep::kSpinSeconds * 1000000000ull;
+  return 0;
+}
 
 extern "C" __attribute__((visibility("default"))) int stm_debug_vsweep_trace(long long *out) {
   return cudaMemcpyFromSymbol(out, vsweep::g_trace, sizeof(long long) * 16 * vsweep::kTraceRows * 4) == cudaSuccess ? 0 : -1;
@@ -885,6 +987,9 @@ int launch_sgm_vsweep_prepare(const float *image, int H, int W, int D, float p1,
   vsweep::sgm_vsweep_penalties<<<(n + 255) / 256, 256, 0, stream>>>(image, pen, H, W, p1, p2);
   return check_launch("sgm_vsweep_penalties");
 }
+
+// stm_sgm_sweep_aborted (include/stm_abi.h)
+int sgm_sweep_aborted(unsigned *info3) { return vsweep::take_sweep_abort(info3); }
 
 // Whether launch_sgm_vsweep will take this shape on the current device.
 bool sgm_vsweep_can_run(int H, int W, int D, int variant_group) {

@@ -12,11 +12,13 @@ fails loudly if the CUDA library has not been built.
 from __future__ import annotations
 
 import ctypes
+import os
 from pathlib import Path
 
 import torch
 
-_LIB_PATH = Path(__file__).resolve().parent / "libstm_b200.so"
+# STM_B200_LIB: developer knob (tools/variant_libs.py: A/B runs of kernel variants on one box)
+_LIB_PATH = Path(os.environ.get("STM_B200_LIB") or Path(__file__).resolve().parent / "libstm_b200.so").resolve()
 
 STM_SGM_MIN_ALL_D = 1
 STM_SGM_OVERWRITE = 2
@@ -52,6 +54,8 @@ _lib.stm_sgm_wta_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _u, _vp
 _lib.stm_dp_f32.argtypes = [_vp, _vp, _vp, _vp, _i, _i, _i, _u, _vp]
 _lib.stm_sgm_pass_timing.argtypes = [_i]
 _lib.stm_sgm_last_pass_ms.argtypes = [_vp, _vp, _i]
+_lib.stm_sgm_sweep_aborted.argtypes = [_vp]
+_lib.stm_sgm_sweep_aborted.restype = _i
 _lib.stm_pipeline_host_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _u, _i, _u]
 _pp = ctypes.POINTER
 _lib.stm_texture_create.argtypes = [_vp, _i, _i, _i, _i, _i, _i, _pp(_vp)]
@@ -339,6 +343,17 @@ class AggregationOps:
         """New (measurement): record CUDA events around each direction pass of the following
         run_semiglobal / run_semiglobal_wta calls (include/stm_abi.h, stm_sgm_pass_timing)."""
         _check(_lib.stm_sgm_pass_timing(1 if enable else 0))
+
+    @staticmethod
+    def sweep_aborted():
+        """New: None, or (CTA, row step, site) if a fused sweep on the current device gave up (no
+        progress for 60 s: a fault) since the last call; that call's output is invalid.  Ask after
+        synchronising the stream (include/stm_abi.h, stm_sgm_sweep_aborted)."""
+        info = (ctypes.c_uint * 3)()
+        rc = _lib.stm_sgm_sweep_aborted(info)
+        if rc < 0:
+            _check(rc)
+        return (int(info[0]), int(info[1]), int(info[2])) if rc == 1 else None
 
     @staticmethod
     def last_pass_ms():
