@@ -45,5 +45,5 @@ CMD="python tools/stage_bench.py 1080 1920 128 --reps 1 --warm 0"
 timeout 300 $CMD > $OUT/${TAG}_full_plain.log 2>&1 &&
 timeout 1500 ncu --set full --clock-control none --import-source on \
     -k regex:'sgm_vsweep|sgm_row_kernel|ssd_rows_kernel|ssd_tiled_kernel|birchfield_row|dp_row|wta_vec_kernel' \
-    -c 24 -f -o $OUT/${TAG}_full $CMD > $OUT/${TAG}_full_ncu.log 2>&1
+    -c 32 -f -o $OUT/${TAG}_full $CMD > $OUT/${TAG}_full_ncu.log 2>&1
 echo "ncu full exit=$?"; tail -3 $OUT/${TAG}_full_ncu.log; ls -la $OUT/${TAG}_full.ncu-rep

@@ -1,5 +1,6 @@
 """Per-stage device times (CUDA events, L2-exceeding volumes) -- developer tool.
-    python tools/stage_bench.py [H W D] [--stages ssd,bt,sgm,wta,dp] [--reps N]"""
+    python tools/stage_bench.py [H W D] [--stages ssd,bt,sgm,wta,dp,sgm_wta] [--reps N]
+sgm_wta = aggregation with the argmin folded in and no volume stored: what Pipeline.estimate runs."""
 import argparse
 import json
 import sys
@@ -14,7 +15,7 @@ from oracle import synth  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("shape", nargs="*", type=int, default=[1080, 1920, 128])
-ap.add_argument("--stages", default="ssd,bt,sgm,wta,dp")
+ap.add_argument("--stages", default="ssd,bt,sgm,wta,dp,sgm_wta")
 ap.add_argument("--reps", type=int, default=10)
 ap.add_argument("--warm", type=int, default=3)
 a = ap.parse_args()
@@ -28,7 +29,7 @@ try:
 except Exception:
     peak = 6573.2
 algo = {"ssd": 4 * N + 8 * H * W, "bt": 4 * N + 8 * H * W, "sgm": 8 * N + 4 * H * W,
-        "wta": 4 * N + 4 * H * W, "dp": 5 * N + 5 * H * W + 8 * H * D}
+        "wta": 4 * N + 4 * H * W, "dp": 5 * N + 5 * H * W + 8 * H * D, "sgm_wta": 4 * N + 8 * H * W}
 ssd, bt = stereomatch.cost.SSD(D), stereomatch.cost.Birchfield(D)
 sgm, wta = stereomatch.aggregation.Semiglobal(), stereomatch.disparity_reduce.WinnerTakesAll()
 dp = stereomatch.disparity_reduce.DynamicProgramming()
@@ -36,7 +37,8 @@ cost = ssd(l, r)
 agg = torch.empty_like(cost)
 disp = torch.empty(H, W, dtype=torch.int32, device="cuda")
 fns = {"ssd": lambda: ssd(l, r, cost), "bt": lambda: bt(l, r, agg), "sgm": lambda: sgm(cost, l, agg),
-       "wta": lambda: wta(agg, disp), "dp": lambda: dp(cost, disp)}
+       "wta": lambda: wta(agg, disp), "dp": lambda: dp(cost, disp),
+       "sgm_wta": lambda: sgm.aggregate_and_reduce(cost, l, agg, disp, keep_volume=False)}
 res = {}
 for name in a.stages.split(","):
     fn = fns[name]
