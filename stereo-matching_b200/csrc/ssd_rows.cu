@@ -81,6 +81,11 @@ struct Cfg {
   // (measured: with V_ITEMS = ITEMS / 3 the V role spills and becomes the critical path, 0.36 -> 0.61 ms)
   static constexpr int V_ITEMS = 0;
   static constexpr int H_ITEMS = ITEMS - V_ITEMS;
+  // one streaming item (a whole row pair) per H warp and group where that keeps every H warp busy
+#ifndef STM_SSD_STREAM_PAIRS
+#define STM_SSD_STREAM_PAIRS 1
+#endif
+  static constexpr bool STREAM_PAIRS = STM_SSD_STREAM_PAIRS && V_ITEMS == 0 && PAIRS >= NH;
   // shared memory, in floats: hbuf[2][WIN][TX][DC], rows[3][PAIRS][TXH + RROW] float2
   static constexpr int HBUF = WIN * TX * DC;
   static constexpr int ROWBUF = PAIRS * (TXH + RROW) * 2;
@@ -137,6 +142,68 @@ __device__ __forceinline__ void ssd_rows_item(const float2 *rb, float *hb, int i
   }
 }
 
+// One horizontal work item of the streaming form: row pair p, ALL runs of group buffer `rb`.
+// ssd_rows_item loads 2*WIN-1 columns per run of WIN outputs: consecutive runs share a van Herk block
+// and load it twice (81 instead of 55 column loads per row pair at K = 7, RUNS = 3).  Here the warp
+// walks the blocks of the row pair once: the finished block's suffix sums stay in registers, the next
+// block's values are added into a running prefix as they are combined.  Same additions in the same
+// order as ssd_rows_item (bit-identical), 17 % fewer instructions and 23 % fewer shared-memory
+// wavefronts per group in the H role; one item per H warp and group when PAIRS == NH.
+template <int K, int RUNS, int NH>
+__device__ __forceinline__ void ssd_rows_pair(const float2 *rb, float *hb, int p, int lane, int x0, int d0, int W) {
+  using namespace ssdr;
+  using C = Cfg<K, RUNS, NH>;
+  constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
+  const int dglob = d0 + lane;
+  const float2 *lp = rb + p * (TXH + RROW);                 // + k: image column x0 - K + k
+  const float2 *rp = lp + TXH + (DC - 1) - lane;            // + k: the same column, d0 + lane to the left
+  const int c0 = x0 - K;
+  u64 s[WIN], e[WIN];
+  auto load_block = [&](int b, u64 (&v)[WIN]) {             // block RUNS (the last) has WIN - 1 columns
+#pragma unroll
+    for (int k = 0; k < WIN; ++k) {
+      if (b == RUNS && k == WIN - 1) { v[k] = 0ull; continue; }
+      const u64 l2 = *reinterpret_cast<const u64 *>(lp + b * WIN + k);
+      const u64 r2 = *reinterpret_cast<const u64 *>(rp + b * WIN + k);
+      const u64 df = sub2(l2, r2);
+      v[k] = mul2(df, df);
+    }
+    const int cb = c0 + b * WIN;
+    // warp-uniform: every column of the block lies in [0, W) and right of every disparity
+    const bool interior = cb >= d0 + DC - 1 && cb + WIN - 1 < W;
+    if (!interior) {
+#pragma unroll
+      for (int k = 0; k < WIN; ++k) {
+        const int c = cb + k;
+        if (!(c < W && c - dglob >= 0)) v[k] = 0ull;        // window clipped to [d, W) (reference :40-42)
+      }
+    }
+  };
+  load_block(0, s);
+#pragma unroll
+  for (int i = WIN - 2; i >= 0; --i) s[i] = add2(s[i], s[i + 1]);
+  float *o0 = hb + ((size_t)(2 * p) * TX) * DC + lane;
+  float *o1 = o0 + (size_t)TX * DC;
+#pragma unroll
+  for (int q = 0; q < RUNS; ++q) {
+    load_block(q + 1, e);
+    u64 run = 0ull;
+#pragma unroll
+    for (int j = 0; j < WIN; ++j) {
+      float s0, s1;
+      upk(j == 0 ? s[0] : add2(s[j], run), s0, s1);
+      o0[(q * WIN + j) * DC] = s0;
+      o1[(q * WIN + j) * DC] = s1;
+      run = j == 0 ? e[0] : add2(run, e[j]);                // e[0], e[0]+e[1], ...: the prefix of the next block
+    }
+    if (q + 1 < RUNS) {
+      s[WIN - 1] = e[WIN - 1];
+#pragma unroll
+      for (int i = WIN - 2; i >= 0; --i) s[i] = add2(e[i], s[i + 1]);
+    }
+  }
+}
+
 template <int K, int RUNS, int NH>
 __global__ void __launch_bounds__(ssdr::Cfg<K, RUNS, NH>::THREADS, 1)
 ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right, float *__restrict__ cost,
@@ -167,31 +234,48 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
     // the index arithmetic per element and group: 47 instructions per 4 bytes, a quarter of the
     // kernel's instructions).
     constexpr int ROWLEN = TXH + RROW, NE = (WIN * ROWLEN + C::VTHREADS - 1) / C::VTHREADS;
-    const float *st_col[NE];   // column pointer in image row 0
-    int st_i[NE];              // row within the group; -1: no element (tail) or column outside the image
-    uint32_t st_dst[NE];       // byte offset in a rows buffer
+    uintptr_t st_addr[NE];     // address of the element in group 0 (row ya - K + i; formed as an integer, only
+                               // used for groups whose rows all lie inside the image)
+    uint32_t st_dst[NE];       // byte offset in a rows buffer; bit 31: column outside the image (zero-fill);
+                               // 0xffffffff: no element (tail)
 #pragma unroll
     for (int e = 0; e < NE; ++e) {
       const int idx = tid + e * C::VTHREADS;
       const int i = idx / ROWLEN, col = idx - i * ROWLEN;
       const bool is_left = col < TXH;
       const int c = is_left ? cbase + col : ubase + (col - TXH);
-      st_col[e] = (is_left ? left : right) + min(max(c, 0), W - 1);
-      st_i[e] = (idx < WIN * ROWLEN && c >= 0 && c < W) ? i : -1 - i;  // negative: zero-fill (i = -1 - st_i)
-      st_dst[e] = idx < WIN * ROWLEN ? (uint32_t)((((i >> 1) * ROWLEN + col) * 2 + (i & 1)) * sizeof(float)) : 0xffffffffu;
+      // the column is clamped so that a zero-filling copy (source size 0) still names a valid address
+      st_addr[e] = reinterpret_cast<uintptr_t>((is_left ? left : right) + min(max(c, 0), W - 1)) +
+                   (uintptr_t)((long long)(ya - K + i) * W * (long long)sizeof(float));
+      st_dst[e] = idx < WIN * ROWLEN ? (uint32_t)((((i >> 1) * ROWLEN + col) * 2 + (i & 1)) * sizeof(float)) |
+                                           ((c >= 0 && c < W) ? 0u : 0x80000000u)
+                                     : 0xffffffffu;
     }
     const uint32_t rows_s = (uint32_t)__cvta_generic_to_shared(rows);
     auto stage_group = [&](int g) {
       const uint32_t dst0 = rows_s + (uint32_t)((g % 3) * C::ROWBUF * sizeof(float));
       const int r0 = ya - K + g * WIN;
+      if (r0 >= 0 && r0 + WIN <= H) {
+        // every row of the group is an image row (block-uniform): address = group-0 address + g groups,
+        // 5 instructions per element (the general body below: ~20, a quarter of the V role's stream)
+        const uintptr_t goff = (uintptr_t)((long long)g * WIN * W * (long long)sizeof(float));
 #pragma unroll
-      for (int e = 0; e < NE; ++e) {
-        if (st_dst[e] != 0xffffffffu) {
-          const int i = st_i[e] >= 0 ? st_i[e] : -1 - st_i[e];
-          const int r = r0 + i;
-          const int ok_bytes = (st_i[e] >= 0 && r >= 0 && r < H) ? 4 : 0;
-          const float *src = st_col[e] + (size_t)min(max(r, 0), H - 1) * W;
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + st_dst[e]), "l"(src), "r"(ok_bytes) : "memory");
+        for (int e = 0; e < NE; ++e) {
+          if (st_dst[e] != 0xffffffffu)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + (st_dst[e] & 0x7fffffffu)),
+                         "l"(st_addr[e] + goff), "r"((int)st_dst[e] >= 0 ? 4 : 0) : "memory");
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < NE; ++e) {
+          if (st_dst[e] != 0xffffffffu) {
+            const int i = (tid + e * C::VTHREADS) / ROWLEN;
+            const int r = r0 + i;
+            const int ok_bytes = ((int)st_dst[e] >= 0 && r >= 0 && r < H) ? 4 : 0;
+            // same column, row clamped into the image
+            const uintptr_t src = st_addr[e] + (uintptr_t)((long long)(min(max(r, 0), H - 1) - (ya - K + i)) * W * (long long)sizeof(float));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + (st_dst[e] & 0x7fffffffu)), "l"(src), "r"(ok_bytes) : "memory");
+          }
         }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
@@ -213,17 +297,17 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
 #pragma unroll
       for (int j = 0; j < 4; ++j) ring[i][j] = 0.f;
     float *ocol = cost + ((size_t)x * D + dfirst);   // + y * W * D
+    const size_t rowstride = (size_t)W * D;
 
     for (int g = 0; g <= n_groups; ++g) {
       stage_group(g + 2);
       if (g >= 1 && active) {
         const float *hb = hbuf + (size_t)(((g - 1) & 1) * C::HBUF) + (size_t)xl * DC + 4 * dq;
         const int ybase = ya - WIN + 1 + (g - 1) * WIN;  // output row completed by row 0 of the group
-#pragma unroll
-        for (int i = 0; i < WIN; ++i) {
+        // One row: read the horizontal sums, advance prefix and ring, form the window sum.
+        auto row_sum = [&](int i, float (&out)[4]) {
           const float4 h = *reinterpret_cast<const float4 *>(hb + (size_t)i * TX * DC);
           const float hv[4] = {h.x, h.y, h.z, h.w};
-          float out[4];
 #pragma unroll
           for (int j = 0; j < 4; j += 2) {
             u64 p2 = add2(pk(pre[j], pre[j + 1]), pk(hv[j], hv[j + 1]));
@@ -233,16 +317,36 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
             ring[i][j] = hv[j];
             ring[i][j + 1] = hv[j + 1];
           }
-          const int y = ybase + i;
-          if (y >= ya && y < yb) {  // block-uniform
-            float *o = ocol + (size_t)y * W * D;
-            if (plain) {
-              // streaming (evict-first) store: plain and write-through stores measured 0.43 vs 0.385 ms
-              __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
-            } else {
+        };
+        if (plain && ybase >= ya && ybase + WIN <= yb) {
+          // Every row of the group is an output row of this chunk and none of the four entries needs
+          // a test: no per-row branch and one pointer bump per row.  (The general body below re-did a
+          // 64-bit y*W*D product and four range tests per row: 26 instructions per row on this path
+          // where 9 do the work -- two thirds of the V role's instruction stream.)
+          float *o = ocol + (size_t)ybase * rowstride;
 #pragma unroll
-              for (int j = 0; j < 4; ++j)
-                if (dfirst + j < D) __stcs(o + j, dfirst + j > x ? CUDART_INF_F : out[j]);
+          for (int i = 0; i < WIN; ++i) {
+            float out[4];
+            row_sum(i, out);
+            // streaming (evict-first) store: plain and write-through stores measured 0.43 vs 0.385 ms
+            __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
+            o += rowstride;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < WIN; ++i) {
+            float out[4];
+            row_sum(i, out);
+            const int y = ybase + i;
+            if (y >= ya && y < yb) {  // block-uniform
+              float *o = ocol + (size_t)y * rowstride;
+              if (plain) {
+                __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
+              } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (dfirst + j < D) __stcs(o + j, dfirst + j > x ? CUDART_INF_F : out[j]);
+              }
             }
           }
         }
@@ -271,9 +375,13 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
       if (g < n_groups) {
         const float2 *rb = reinterpret_cast<const float2 *>(rows + (g % 3) * C::ROWBUF);
         float *hb = hbuf + (size_t)((g & 1) * C::HBUF);
-        // items [0, H_ITEMS) belong to the H warps; the V warps take the rest after their own rows
-        for (int item = hw; item < C::H_ITEMS; item += NH)
-          ssd_rows_item<K, RUNS, NH>(rb, hb, item, lane, x0, d0, W);
+        if constexpr (C::STREAM_PAIRS) {
+          for (int pr = hw; pr < PAIRS; pr += NH) ssd_rows_pair<K, RUNS, NH>(rb, hb, pr, lane, x0, d0, W);
+        } else {
+          // items [0, H_ITEMS) belong to the H warps; the V warps take the rest after their own rows
+          for (int item = hw; item < C::H_ITEMS; item += NH)
+            ssd_rows_item<K, RUNS, NH>(rb, hb, item, lane, x0, d0, W);
+        }
       }
       named_barrier(C::THREADS);
     }
