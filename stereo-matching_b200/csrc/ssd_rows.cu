@@ -21,14 +21,21 @@
 // per group; image rows are requested with cp.async two groups ahead.  HBM traffic = the 4 B/pix-disp
 // store of C plus the images.
 //
-// What was measured (1080p D=128, profiles/r02_v6_ssd_investigation.md): 0.350 ms against 0.371 for
-// ssd_tiled_kernel -- a small gain for a kernel with far fewer arithmetic instructions, because
-// instruction issue was not the limit after all.  A store-only kernel with exactly this write
-// pattern (128-byte chunks of each pixel's vector from four CTAs) runs in 0.164 ms, so the pattern
-// is not the limit either.  What is left is the single CTA per SM (174 KB of shared memory) with
-// its two roles meeting at a barrier, and ~2700 shared-memory wavefronts per group.  Variants that
-// were measured and are worse: plain instead of streaming stores (0.43), 11 H warps (0.46, spills),
-// V warps helping with H items (0.61, spills).
+// What was measured (1080p D=128, profiles/r02_v6_ssd_investigation.md).  First version: 0.350 ms
+// against 0.371 for ssd_tiled_kernel.  A store-only kernel with exactly this write pattern
+// (128-byte chunks of each pixel's vector from four CTAs) runs in 0.164 ms, so the pattern is not the
+// limit.  r02 v11 (ncu per-line counts, profiles/r02_v11_ssd_ncu.md): two thirds of the V role's
+// instruction stream were a 64-bit y*W*D product and four range tests per row, and the H warps
+// loaded every van Herk block twice (once per adjacent run): branch-free row loop with a pointer
+// bump, staging with one add per element, and STREAMING row-pair items (ssd_rows_pair: each block
+// loaded once, square and sum as one packed FMA, left values as 16-byte broadcast loads)
+// -> 0.349 -> 0.282 ms (D=192: 0.499 -> 0.388).  The kernel is now bound by the shared-memory /
+// LSU data path: 73 % of its wavefront slots are busy (5.1 wavefronts per 128 bytes of C: one for
+// the global store, two for the H -> V hand-off, two for the image values), 18 % of the warp
+// samples wait at the role barrier.  Variants that were measured and are worse: plain instead of
+// streaming stores (0.43), 11 H warps (0.46, spills), V warps helping with H items (0.61, spills),
+// 8 / 9 H warps (0.328 / 0.362), staging dealt out statically per V warp (6 registers of state
+// instead of 18, no spills, but 0.310: eleven unrolled variants of the staging code).
 #include <cstdlib>
 
 #include "stm_common.cuh"
@@ -59,6 +66,11 @@ __device__ __forceinline__ u64 sub2(u64 a, u64 b) {
   asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+  u64 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
 __device__ __forceinline__ u64 mul2(u64 a, u64 b) {
   u64 d;
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
@@ -86,9 +98,10 @@ struct Cfg {
 #define STM_SSD_STREAM_PAIRS 1
 #endif
   static constexpr bool STREAM_PAIRS = STM_SSD_STREAM_PAIRS && V_ITEMS == 0 && PAIRS >= NH;
-  // shared memory, in floats: hbuf[2][WIN][TX][DC], rows[3][PAIRS][TXH + RROW] float2
+  // shared memory, in floats: hbuf[2][WIN][TX][DC], rows[3][PAIRS][RSTRIDE] float2
   static constexpr int HBUF = WIN * TX * DC;
-  static constexpr int ROWBUF = PAIRS * (TXH + RROW) * 2;
+  static constexpr int RSTRIDE = (TXH + RROW + 1) & ~1;   // float2 per staged row pair; even: 16-byte loads of two columns
+  static constexpr int ROWBUF = PAIRS * RSTRIDE * 2;
   static constexpr size_t SMEM = (size_t)(2 * HBUF + 3 * ROWBUF) * sizeof(float);
 };
 
@@ -106,8 +119,8 @@ __device__ __forceinline__ void ssd_rows_item(const float2 *rb, float *hb, int i
   constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
   const int dglob = d0 + lane;
   const int p = item / RUNS, q = item - p * RUNS;
-  const float2 *lp = rb + p * (TXH + RROW) + q * WIN;                          // + k
-  const float2 *rp = rb + p * (TXH + RROW) + TXH + q * WIN + (DC - 1) - lane;  // + k
+  const float2 *lp = rb + p * C::RSTRIDE + q * WIN;                            // + k
+  const float2 *rp = rb + p * C::RSTRIDE + TXH + q * WIN + (DC - 1) - lane;    // + k
   const int c0 = x0 + q * WIN - K;  // image column of k = 0
   // warp-uniform: every column of the item lies in [0, W) and right of every disparity
   const bool interior = c0 >= d0 + DC - 1 && c0 + 2 * WIN - 2 < W;
@@ -155,18 +168,27 @@ __device__ __forceinline__ void ssd_rows_pair(const float2 *rb, float *hb, int p
   using C = Cfg<K, RUNS, NH>;
   constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
   const int dglob = d0 + lane;
-  const float2 *lp = rb + p * (TXH + RROW);                 // + k: image column x0 - K + k
+  const float2 *lp = rb + p * C::RSTRIDE;                   // + k: image column x0 - K + k
   const float2 *rp = lp + TXH + (DC - 1) - lane;            // + k: the same column, d0 + lane to the left
   const int c0 = x0 - K;
-  u64 s[WIN], e[WIN];
+  // s: suffix sums of the finished block; f: the DIFFERENCES of the next block.  Their squares are
+  // never formed on their own: each one enters a sum, so the square and the addition are one packed
+  // FMA (exact, hence bit-identical to mul + add, for integer-valued images; one rounding instead of
+  // two -- a last-bit difference -- otherwise).
+  u64 s[WIN], f[WIN];
   auto load_block = [&](int b, u64 (&v)[WIN]) {             // block RUNS (the last) has WIN - 1 columns
+    static_assert(WIN % 2 == 0, "two columns per 16-byte load");
 #pragma unroll
-    for (int k = 0; k < WIN; ++k) {
-      if (b == RUNS && k == WIN - 1) { v[k] = 0ull; continue; }
-      const u64 l2 = *reinterpret_cast<const u64 *>(lp + b * WIN + k);
-      const u64 r2 = *reinterpret_cast<const u64 *>(rp + b * WIN + k);
-      const u64 df = sub2(l2, r2);
-      v[k] = mul2(df, df);
+    for (int k = 0; k < WIN; k += 2) {
+      // the left values are the same for every lane: one 16-byte broadcast load fetches two columns
+      // (both rows each); the last pair of the last block reads one staged column past the left ones
+      const ulonglong2 l4 = *reinterpret_cast<const ulonglong2 *>(lp + b * WIN + k);
+#pragma unroll
+      for (int kk = 0; kk < 2; ++kk) {
+        if (b == RUNS && k + kk == WIN - 1) { v[k + kk] = 0ull; continue; }
+        const u64 r2 = *reinterpret_cast<const u64 *>(rp + b * WIN + k + kk);
+        v[k + kk] = sub2(kk ? l4.y : l4.x, r2);
+      }
     }
     const int cb = c0 + b * WIN;
     // warp-uniform: every column of the block lies in [0, W) and right of every disparity
@@ -179,14 +201,15 @@ __device__ __forceinline__ void ssd_rows_pair(const float2 *rb, float *hb, int p
       }
     }
   };
-  load_block(0, s);
+  load_block(0, f);
+  s[WIN - 1] = mul2(f[WIN - 1], f[WIN - 1]);
 #pragma unroll
-  for (int i = WIN - 2; i >= 0; --i) s[i] = add2(s[i], s[i + 1]);
+  for (int i = WIN - 2; i >= 0; --i) s[i] = fma2(f[i], f[i], s[i + 1]);
   float *o0 = hb + ((size_t)(2 * p) * TX) * DC + lane;
   float *o1 = o0 + (size_t)TX * DC;
 #pragma unroll
   for (int q = 0; q < RUNS; ++q) {
-    load_block(q + 1, e);
+    load_block(q + 1, f);
     u64 run = 0ull;
 #pragma unroll
     for (int j = 0; j < WIN; ++j) {
@@ -194,12 +217,12 @@ __device__ __forceinline__ void ssd_rows_pair(const float2 *rb, float *hb, int p
       upk(j == 0 ? s[0] : add2(s[j], run), s0, s1);
       o0[(q * WIN + j) * DC] = s0;
       o1[(q * WIN + j) * DC] = s1;
-      run = j == 0 ? e[0] : add2(run, e[j]);                // e[0], e[0]+e[1], ...: the prefix of the next block
+      run = j == 0 ? mul2(f[0], f[0]) : fma2(f[j], f[j], run);   // the prefix of the next block
     }
     if (q + 1 < RUNS) {
-      s[WIN - 1] = e[WIN - 1];
+      s[WIN - 1] = mul2(f[WIN - 1], f[WIN - 1]);
 #pragma unroll
-      for (int i = WIN - 2; i >= 0; --i) s[i] = add2(e[i], s[i + 1]);
+      for (int i = WIN - 2; i >= 0; --i) s[i] = fma2(f[i], f[i], s[i + 1]);
     }
   }
 }
@@ -213,7 +236,7 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
   constexpr int WIN = C::WIN, PAIRS = C::PAIRS, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
   extern __shared__ __align__(16) float smem[];
   float *hbuf = smem;                 // [(b*WIN + row)*TX + x][DC]
-  float *rows = smem + 2 * C::HBUF;   // [b3][pair][TXH + RROW] float2: left columns, then right columns
+  float *rows = smem + 2 * C::HBUF;   // [b3][pair][RSTRIDE] float2: left columns, then right columns
 
   const int tid = threadIdx.x;
   const int x0 = (d_fastest ? blockIdx.y : blockIdx.x) * TX;
@@ -247,7 +270,7 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
       // the column is clamped so that a zero-filling copy (source size 0) still names a valid address
       st_addr[e] = reinterpret_cast<uintptr_t>((is_left ? left : right) + min(max(c, 0), W - 1)) +
                    (uintptr_t)((long long)(ya - K + i) * W * (long long)sizeof(float));
-      st_dst[e] = idx < WIN * ROWLEN ? (uint32_t)((((i >> 1) * ROWLEN + col) * 2 + (i & 1)) * sizeof(float)) |
+      st_dst[e] = idx < WIN * ROWLEN ? (uint32_t)((((i >> 1) * C::RSTRIDE + col) * 2 + (i & 1)) * sizeof(float)) |
                                            ((c >= 0 && c < W) ? 0u : 0x80000000u)
                                      : 0xffffffffu;
     }
