@@ -395,8 +395,41 @@ def run_b200_arm(args):
         torch.cuda.synchronize()
         return rec
 
+    def run_config1(Hc, Wc, Dc, label, l2_note=None):
+        """BASELINE.json config 1 in its GPU form: SSD + WTA without aggregation -- two stages with the
+        volume in HBM, and the single pass that never writes it (stm_ssd_wta_f32, what Pipeline runs)."""
+        from oracle import synth
+        lh, rh, _ = synth.random_dot_pair(Hc, Wc, Dc, seed=1000, scale="raw")
+        lc, rc = torch.from_numpy(lh).to(dev), torch.from_numpy(rh).to(dev)
+        n_pd = Hc * Wc * Dc
+        cost_op = stereomatch.cost.SSD(Dc, KERNEL_SIZE)
+        wt = stereomatch.disparity_reduce.WinnerTakesAll()
+        cvol = cost_op(lc, rc)
+        dimg = wt(cvol)
+        rec = {"shape": f"{Wc}x{Hc} D={Dc}", "stages": {}}
+        rec["stages"]["ssd"] = stage_record(stage_ms(lambda: cost_op(lc, rc, cost_volume=cvol)), 4.0 + 8.0 / Dc, n_pd)
+        rec["stages"]["wta"] = stage_record(stage_ms(lambda: wt(cvol, dimg)), 4.0 + 4.0 / Dc, n_pd)
+        p_ = stereomatch.Pipeline(cost_op, wt)
+        p_._disparity_image = dimg
+        fused = stage_ms(lambda: p_.estimate(lc, rc))
+        rec["frame"] = {"ms": round(fused, 4), "Gpix_disp_s": round(n_pd / (fused * 1e-3) / 1e9, 2),
+                        "hbm_bytes_per_pixel": 28,
+                        "note": "Pipeline.estimate = one pass, no volume (stm_ssd_wta_f32); device-resident"}
+        p_.fuse_cost_and_reduce = False
+        p_._cost_volume = cvol
+        two = stage_ms(lambda: p_.estimate(lc, rc))
+        rec["frame_two_stages"] = {"ms": round(two, 4), "Gpix_disp_s": round(n_pd / (two * 1e-3) / 1e9, 2)}
+        if l2_note:
+            rec["l2"] = l2_note
+        rec["workload"] = label
+        torch.cuda.synchronize()
+        return rec
+
     configs = {}
     if not args.no_configs:
+        configs["config1_gpu"] = run_config1(375, 450, 64, "450x375 D=64 SSD+WTA, no aggregation (GPU form of config 1)",
+                                             l2_note="L2-resident (43 MB volume): not HBM-roofline evidence")
+        configs["config1_gpu_1080p"] = run_config1(H, W, D, "1920x1080 D=128 SSD+WTA, no aggregation")
         configs["config2"] = run_config(375, 450, 64, "ssd", "wta", "450x375 D=64 SSD+SGM+WTA",
                                         l2_note="L2-resident (43 MB volumes): not HBM-roofline evidence")
         configs["config3"] = run_config(H, W, D, "birchfield", "wta", "1920x1080 D=128 Birchfield+SGM+WTA")

@@ -116,6 +116,20 @@ int stm_birchfield_f32(const float *left, const float *right, float *cost, int H
 int stm_birchfield_wta_f32(const float *left, const float *right, int32_t *disparity, int H, int W,
                            int D, void *stream);
 
+/* SSD cost and winner-takes-all in one pass, the volume never written: what Pipeline.estimate does
+ * for SSD + WinnerTakesAll WITHOUT aggregation (reference stereomatch/pipeline.py:80-92 chains
+ * compute_ssd, src/cost.cpp:9, and run_winners_take_all, src/disparity_reduce.cpp:6-9; BASELINE.json
+ * config 1 in its GPU form).  The disparity map is exactly stm_wta_f32 of stm_ssd_f32's volume (tested):
+ * the threads that would store a pixel's 128-byte chunk of C send one (cost, disparity) key per pixel and
+ * disparity chunk to `scratch` with a 64-bit atomic minimum instead; a second small kernel writes the
+ * int32 map.  HBM traffic is 28 bytes per PIXEL instead of 8 bytes per pixel-disparity.
+ * `scratch`: stm_ssd_wta_scratch_bytes(H, W) bytes of device memory (H*W 64-bit words; contents
+ * irrelevant on entry, garbage on exit).  kernel_size 7 or 3 and D % 4 == 0 only; other shapes return
+ * STM_EUNSUPPORTED (the binding then runs the two stages).  New, SURVEY.md 8(f) N1. */
+size_t stm_ssd_wta_scratch_bytes(int H, int W);
+int stm_ssd_wta_f32(const float *left, const float *right, int32_t *disparity, int H, int W, int D,
+                    int kernel_size, void *scratch, size_t scratch_bytes, void *stream);
+
 /* Replaces AggregationOps.run_semiglobal(cost, left_image, p1, p2, out)
  * (reference src/aggregation.cpp:6 -> AggregationOps::RunSemiglobal, src/semiglobal.cpp:167-197).
  * Aggregates over the reference path set (8 directions, including its stored-end quirk)

@@ -17,6 +17,7 @@ int launch_wta(const float *, int32_t *, int, int, int, cudaStream_t);
 int launch_ssd(const float *, const float *, float *, int, int, int, int, cudaStream_t);
 int launch_birchfield(const float *, const float *, float *, int, int, int, cudaStream_t);
 int launch_birchfield_wta(const float *, const float *, int32_t *, int, int, int, cudaStream_t);
+int launch_ssd_wta(const float *, const float *, int32_t *, unsigned long long *, int, int, int, int, cudaStream_t);
 size_t sgm_workspace_bytes(int, int, int);
 size_t sgm_workspace_bytes_flags(int, int, int, unsigned);
 int sgm_sweep_aborted(unsigned *);  // sgm_vsweep.cu
@@ -114,6 +115,27 @@ int stm_birchfield_wta_f32(const float *left, const float *right, int32_t *dispa
   if (rc == 1)
     return fail(STM_EUNSUPPORTED, "birchfield_wta: needs D %% 64 == 0 and 8 <= W <= ~6000 (got W=%d D=%d); "
                 "use stm_birchfield_f32 + stm_wta_f32", W, D);
+  return rc;
+}
+
+size_t stm_ssd_wta_scratch_bytes(int H, int W) {
+  if (H <= 0 || W <= 0) return 0;
+  return (size_t)H * W * sizeof(unsigned long long);
+}
+
+int stm_ssd_wta_f32(const float *left, const float *right, int32_t *disparity, int H, int W, int D,
+                    int kernel_size, void *scratch, size_t scratch_bytes, void *stream) {
+  int rc = check_shape("ssd_wta", H, W, D);
+  if (rc) return rc;
+  STM_REQUIRE(left && right && disparity && scratch, "ssd_wta: null pointer");
+  STM_REQUIRE(scratch_bytes >= stm_ssd_wta_scratch_bytes(H, W), "ssd_wta: scratch too small");
+  STM_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 7) == 0, "ssd_wta: scratch must be 8-byte aligned");
+  if ((rc = require_device())) return rc;
+  rc = launch_ssd_wta(left, right, disparity, static_cast<unsigned long long *>(scratch), H, W, D, kernel_size,
+                      (cudaStream_t)stream);
+  if (rc == 1)
+    return fail(STM_EUNSUPPORTED, "ssd_wta: needs kernel_size 7 or 3 and D %% 4 == 0 (got k=%d D=%d); "
+                "use stm_ssd_f32 + stm_wta_f32", kernel_size, D);
   return rc;
 }
 

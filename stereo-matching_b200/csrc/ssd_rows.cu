@@ -116,7 +116,7 @@ template <int K, int RUNS, int NH>
 __device__ __forceinline__ void ssd_rows_item(const float2 *rb, float *hb, int item, int lane, int x0, int d0, int W) {
   using namespace ssdr;
   using C = Cfg<K, RUNS, NH>;
-  constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
+  constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC;
   const int dglob = d0 + lane;
   const int p = item / RUNS, q = item - p * RUNS;
   const float2 *lp = rb + p * C::RSTRIDE + q * WIN;                            // + k
@@ -166,7 +166,7 @@ template <int K, int RUNS, int NH>
 __device__ __forceinline__ void ssd_rows_pair(const float2 *rb, float *hb, int p, int lane, int x0, int d0, int W) {
   using namespace ssdr;
   using C = Cfg<K, RUNS, NH>;
-  constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
+  constexpr int WIN = C::WIN, TX = C::TX, TXH = C::TXH, DC = C::DC;
   const int dglob = d0 + lane;
   const float2 *lp = rb + p * C::RSTRIDE;                   // + k: image column x0 - K + k
   const float2 *rp = lp + TXH + (DC - 1) - lane;            // + k: the same column, d0 + lane to the left
@@ -227,10 +227,15 @@ __device__ __forceinline__ void ssd_rows_pair(const float2 *rb, float *hb, int p
   }
 }
 
-template <int K, int RUNS, int NH>
+// WTA = true (stm_ssd_wta_f32): the V threads do not store C; they take the first minimum of their
+// four entries, combine the eight threads of a pixel by shuffles and send one 64-bit key
+// (cost bits << 32 | disparity) per pixel, row and disparity chunk to `keys` with an atomic minimum:
+// costs are >= +0, so the unsigned order of the keys is (cost, then disparity) -- the first-minimum
+// rule of wta.cu / reference src/winners_take_all.cu:21-40 across the chunks of all CTAs.
+template <int K, int RUNS, int NH, bool WTA>
 __global__ void __launch_bounds__(ssdr::Cfg<K, RUNS, NH>::THREADS, 1)
 ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right, float *__restrict__ cost,
-                int H, int W, int D, int rows_per_chunk, int d_fastest) {
+                unsigned long long *__restrict__ keys, int H, int W, int D, int rows_per_chunk, int d_fastest) {
   using namespace ssdr;
   using C = Cfg<K, RUNS, NH>;
   constexpr int WIN = C::WIN, PAIRS = C::PAIRS, TX = C::TX, TXH = C::TXH, DC = C::DC, RROW = C::RROW;
@@ -313,6 +318,12 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
     const bool active = xl < TX && x < W;
     const int dfirst = d0 + 4 * dq;
     const bool plain = active && dfirst + 3 < D && dfirst + 3 <= x;   // nothing to test per element
+    // WTA: the threads of a warp shuffle with the FULL mask, so a warp branches as one: its four pixels
+    // x_w .. x_w + 3 all exist and need no test.  (Shuffles under the 8-lane mask of a pixel split the
+    // warp into four groups that then run the row loop one after the other: 0.49 ms instead of 0.3.)
+    const int xw = x0 + (tid >> 5) * 4;
+    const bool warp_has_pixels = (tid >> 5) * 4 < TX && xw < W;
+    const bool warp_plain = (tid >> 5) * 4 + 3 < TX && xw + 3 < W && d0 + DC - 1 < D && d0 + DC - 1 <= xw;
     float ring[WIN][4];
     float pre[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -321,11 +332,39 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
       for (int j = 0; j < 4; ++j) ring[i][j] = 0.f;
     float *ocol = cost + ((size_t)x * D + dfirst);   // + y * W * D
     const size_t rowstride = (size_t)W * D;
+    // WTA: one key per pixel, row and disparity chunk.  `bounded` = entries d > x (+inf) or d >= D
+    // (absent) have to be skipped.
+    auto emit_key = [&](int y, const float (&out)[4], bool bounded) {
+      float best = CUDART_INF_F;
+      unsigned bd = (unsigned)dfirst;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int d = dfirst + j;
+        if ((!bounded || (d < D && d <= x)) && out[j] < best) {  // strict: the lowest d keeps a tie; NaN never wins
+          best = out[j];
+          bd = (unsigned)d;
+        }
+      }
+      unsigned hi = __float_as_uint(best), lo = bd;
+      if (dfirst == 0 && out[0] != out[0]) hi = 0u;              // NaN at d = 0: the reference answers 0
+      if (dfirst >= D || !active) { hi = 0xffffffffu; lo = 0xffffffffu; }   // padding of the last chunk / no pixel
+      // The minimum cost of the pixel's eight threads by three shuffles of the cost bits; every thread that
+      // holds it sends its key (normally one; on a tie the atomic keeps the lowest disparity).  Measured
+      // at 1080p D=128: a butterfly over (cost, d) pairs -- six shuffles per row through the already
+      // saturated LSU/MIO path -- 0.516 ms (0.354 without any shuffle, 0.485 without the atomics);
+      // electing the owner with a vote, 0.75 ms, and redux.sync.min.u32, 0.82 ms: both are slow with
+      // the four 8-lane masks of a warp.
+      unsigned m = hi;
+#pragma unroll
+      for (int w = 1; w < 8; w <<= 1) m = min(m, __shfl_xor_sync(FULL, m, w));   // stays inside the pixel's 8 lanes
+      if (hi == m && active) atomicMin(keys + ((size_t)y * W + x), ((unsigned long long)hi << 32) | lo);
+    };
 
     for (int g = 0; g <= n_groups; ++g) {
       stage_group(g + 2);
-      if (g >= 1 && active) {
-        const float *hb = hbuf + (size_t)(((g - 1) & 1) * C::HBUF) + (size_t)xl * DC + 4 * dq;
+      if (g >= 1 && (WTA ? warp_has_pixels : active)) {
+        // (WTA: a thread without a pixel reads the tile's last column and sends nothing)
+        const float *hb = hbuf + (size_t)(((g - 1) & 1) * C::HBUF) + (size_t)(WTA ? min(xl, TX - 1) : xl) * DC + 4 * dq;
         const int ybase = ya - WIN + 1 + (g - 1) * WIN;  // output row completed by row 0 of the group
         // One row: read the horizontal sums, advance prefix and ring, form the window sum.
         auto row_sum = [&](int i, float (&out)[4]) {
@@ -341,19 +380,23 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
             ring[i][j + 1] = hv[j + 1];
           }
         };
-        if (plain && ybase >= ya && ybase + WIN <= yb) {
+        if ((WTA ? warp_plain : plain) && ybase >= ya && ybase + WIN <= yb) {
           // Every row of the group is an output row of this chunk and none of the four entries needs
           // a test: no per-row branch and one pointer bump per row.  (The general body below re-did a
           // 64-bit y*W*D product and four range tests per row: 26 instructions per row on this path
           // where 9 do the work -- two thirds of the V role's instruction stream.)
-          float *o = ocol + (size_t)ybase * rowstride;
+          float *o = WTA ? nullptr : ocol + (size_t)ybase * rowstride;
 #pragma unroll
           for (int i = 0; i < WIN; ++i) {
             float out[4];
             row_sum(i, out);
-            // streaming (evict-first) store: plain and write-through stores measured 0.43 vs 0.385 ms
-            __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
-            o += rowstride;
+            if constexpr (WTA) {
+              emit_key(ybase + i, out, false);
+            } else {
+              // streaming (evict-first) store: plain and write-through stores measured 0.43 vs 0.385 ms
+              __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
+              o += rowstride;
+            }
           }
         } else {
 #pragma unroll
@@ -362,6 +405,10 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
             row_sum(i, out);
             const int y = ybase + i;
             if (y >= ya && y < yb) {  // block-uniform
+              if constexpr (WTA) {
+                emit_key(y, out, true);
+                continue;
+              }
               float *o = ocol + (size_t)y * rowstride;
               if (plain) {
                 __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
@@ -411,15 +458,15 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
   }
 }
 
-template <int K, int RUNS, int NH>
-static int run_ssd_rows(const float *left, const float *right, float *cost, int H, int W, int D,
-                        cudaStream_t stream) {
+template <int K, int RUNS, int NH, bool WTA>
+static int run_ssd_rows(const float *left, const float *right, float *cost, unsigned long long *keys, int H, int W,
+                        int D, cudaStream_t stream) {
   using C = ssdr::Cfg<K, RUNS, NH>;
   static PerDeviceInt configured;  // the > 48 KB opt-in is per function AND per device
   const int dev = device_slot();
   int done = 0;
   if (!configured.get(dev, &done)) {
-    if (cudaFuncSetAttribute(ssd_rows_kernel<K, RUNS, NH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (cudaFuncSetAttribute(ssd_rows_kernel<K, RUNS, NH, WTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)C::SMEM) != cudaSuccess) {
       cudaGetLastError();
       return 1;  // the caller runs ssd_tiled_kernel
@@ -444,7 +491,7 @@ static int run_ssd_rows(const float *left, const float *right, float *cost, int 
   const int d_fastest = !(order && order[0] == 'x');
   if (nx > 65535) return fail(STM_EUNSUPPORTED, "ssd: shape too large");
   const dim3 grid = d_fastest ? dim3(nd, nx, ny) : dim3(nx, nd, ny);
-  ssd_rows_kernel<K, RUNS, NH><<<grid, C::THREADS, C::SMEM, stream>>>(left, right, cost, H, W, D, rows, d_fastest);
+  ssd_rows_kernel<K, RUNS, NH, WTA><<<grid, C::THREADS, C::SMEM, stream>>>(left, right, cost, keys, H, W, D, rows, d_fastest);
   return check_launch("ssd_rows_kernel");
 }
 
@@ -457,10 +504,29 @@ int launch_ssd_rows(const float *left, const float *right, float *cost, int H, i
     if (off && off[0] == '0') return 1;
   }
   switch (k) {
-    case 7: return run_ssd_rows<7, 3, STM_SSD_NH7>(left, right, cost, H, W, D, stream);
-    case 3: return run_ssd_rows<3, 8, 8>(left, right, cost, H, W, D, stream);
+    case 7: return run_ssd_rows<7, 3, STM_SSD_NH7, false>(left, right, cost, nullptr, H, W, D, stream);
+    case 3: return run_ssd_rows<3, 8, 8, false>(left, right, cost, nullptr, H, W, D, stream);
     default: return 1;
   }
+}
+
+__global__ void ssd_wta_extract_kernel(const unsigned long long *__restrict__ keys, int32_t *__restrict__ disp, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) disp[i] = (int32_t)(unsigned)(keys[i] & 0xffffffffull);
+}
+
+// SSD cost + winner-takes-all without the volume (stm_ssd_wta_f32).  `keys` = H*W 64-bit words of scratch.
+// Returns 0 on success, 1 when the shape is not handled (k not 7 / 3, D % 4 != 0).
+int launch_ssd_wta(const float *left, const float *right, int32_t *disp, unsigned long long *keys, int H, int W,
+                   int D, int k, cudaStream_t stream) {
+  if (D % 4 != 0 || (k != 7 && k != 3)) return 1;
+  const size_t n = (size_t)H * W;
+  STM_CUDA_TRY(cudaMemsetAsync(keys, 0xff, n * sizeof(unsigned long long), stream));
+  const int rc = k == 7 ? run_ssd_rows<7, 3, STM_SSD_NH7, true>(left, right, nullptr, keys, H, W, D, stream)
+                        : run_ssd_rows<3, 8, 8, true>(left, right, nullptr, keys, H, W, D, stream);
+  if (rc) return rc;
+  ssd_wta_extract_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(keys, disp, n);
+  return check_launch("ssd_wta_extract_kernel");
 }
 
 }  // namespace stm

@@ -44,6 +44,10 @@ _lib.stm_ssd_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _vp]
 _lib.stm_birchfield_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _vp]
 _lib.stm_birchfield_wta_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _vp]
 _lib.stm_birchfield_wta_f32.restype = _i
+_lib.stm_ssd_wta_scratch_bytes.argtypes = [_i, _i]
+_lib.stm_ssd_wta_scratch_bytes.restype = _sz
+_lib.stm_ssd_wta_f32.argtypes = [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _sz, _vp]
+_lib.stm_ssd_wta_f32.restype = _i
 _lib.stm_sgm_workspace_bytes.argtypes = [_i, _i, _i]
 _lib.stm_sgm_workspace_bytes.restype = _sz
 _lib.stm_sgm_workspace_bytes_flags.argtypes = [_i, _i, _i, _u]
@@ -293,6 +297,30 @@ class CostOps:
             _check(_lib.stm_birchfield_f32(left.data_ptr(), right.data_ptr(), cost.data_ptr(), H, W,
                                            cost.shape[2], _stream()))
 
+
+    @staticmethod
+    def compute_ssd_wta(left_image, right_image, disparity_image, max_disparity: int, kernel_size: int) -> bool:
+        """New: compute_ssd + run_winners_take_all in one pass, the volume never written
+        (include/stm_abi.h, stm_ssd_wta_f32).  Returns False when the shape is not supported
+        (kernel_size not 7 / 3, D % 4 != 0): the caller then runs the two stages."""
+        left = _gpu("SSDKernel: left_image", left_image, torch.float32, 2)
+        right = _gpu("SSDKernel: right_image", right_image, torch.float32, 2, left)
+        disp = _out("disparity_image",
+                    _gpu("RunWinnersTakeAll: disparity_image", disparity_image, torch.int32, 2, left))
+        if right.shape != left.shape or disp.shape != left.shape:
+            raise RuntimeError("SSDKernel: image / disparity shapes do not match")
+        left, right = left.contiguous(), right.contiguous()
+        H, W = left.shape
+        nbytes = int(_lib.stm_ssd_wta_scratch_bytes(H, W))
+        scratch = _sgm_workspace(left.device, nbytes)   # per (device, stream), shared with the SGM workspace
+        with torch.cuda.device(left.device):
+            rc = _lib.stm_ssd_wta_f32(left.data_ptr(), right.data_ptr(), disp.data_ptr(), H, W,
+                                      int(max_disparity), int(kernel_size), scratch.data_ptr(), scratch.numel(),
+                                      _stream())
+        if rc == -3:   # STM_EUNSUPPORTED
+            return False
+        _check(rc)
+        return True
 
     @staticmethod
     def compute_birchfield_wta(left_image, right_image, disparity_image, max_disparity: int) -> bool:

@@ -32,6 +32,21 @@ class SSD:
         _CostOps.compute_ssd(left_image, right_image, cost_volume, self.kernel_size)
         return cost_volume
 
+    def cost_and_reduce(self, left_image: torch.Tensor, right_image: torch.Tensor,
+                        disparity_img: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        """New: SSD cost followed by winner-takes-all in one pass; the cost volume is never written
+        (28 bytes of HBM traffic per pixel instead of 8 per pixel-disparity).  Returns the int32
+        disparity map -- exactly WinnerTakesAll()(self(left, right)) -- or None when the shape is
+        not supported (kernel_size not 7 / 3, max_disparity % 4 != 0), in which case the caller
+        runs the two stages."""
+        if self.cost_volume_dtype not in (torch.float, torch.float32):
+            return None
+        disparity_img = empty_tensor(left_image.size(0), left_image.size(1), dtype=torch.int32,
+                                     device=left_image.device, reuse_tensor=disparity_img)
+        ok = _CostOps.compute_ssd_wta(left_image, right_image, disparity_img, self.max_disparity,
+                                      self.kernel_size)
+        return disparity_img if ok else None
+
 
 class SSDTexture:
     """SSD over CUDA texture inputs (reference stereomatch/cost.py:51-77): same volume as SSD on

@@ -4,7 +4,7 @@ from typing import Callable, Optional
 import torch
 
 from .aggregation import Semiglobal
-from .cost import Birchfield, SSDTexture
+from .cost import SSD, Birchfield, SSDTexture
 from .cuda_texture import CUDATexture
 from .disparity_reduce import WinnerTakesAll
 
@@ -63,9 +63,10 @@ class Pipeline:
                 return self.estimate(left_image, right_image)
             finally:
                 self._disparity_image = keep
-        if (self.fuse_cost_and_reduce and self.aggregation is None and type(self.cost) is Birchfield
+        if (self.fuse_cost_and_reduce and self.aggregation is None and type(self.cost) in (Birchfield, SSD)
                 and type(self.disparity_reduce) is WinnerTakesAll):
-            # cost + reduce in one kernel, the volume never materialised (stm_birchfield_wta_f32)
+            # cost + reduce in one pass, the volume never materialised (stm_birchfield_wta_f32,
+            # stm_ssd_wta_f32)
             fused = self.cost.cost_and_reduce(left_image, right_image, self._disparity_image)
             if fused is not None:
                 self._disparity_image = fused

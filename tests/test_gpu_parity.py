@@ -614,6 +614,47 @@ def test_birchfield_with_winner_takes_all_folded_in(sm, H, W, D, scale):
     assert torch.equal(p48.estimate(l, r), sm.disparity_reduce.WinnerTakesAll()(sm.cost.Birchfield(48)(l, r)))
 
 
+@pytest.mark.parametrize("H,W,D,k,scale", [(21, 45, 64, 7, "unit"), (33, 150, 128, 7, "raw"), (40, 70, 192, 7, "raw"),
+                                            (17, 203, 256, 3, "unit"), (30, 9, 64, 7, "raw"), (12, 50, 36, 7, "raw"),
+                                            (64, 96, 4, 3, "raw"), (375, 450, 64, 7, "raw"), (1080, 1920, 128, 7, "raw")])
+def test_ssd_with_winner_takes_all_folded_in(sm, H, W, D, k, scale):
+    """stm_ssd_wta_f32: the map is EXACTLY WinnerTakesAll of the SSD volume (same kernel arithmetic,
+    first-minimum rule across the disparity chunks of different CTAs, +inf for d > x), without the
+    volume being written; Pipeline(SSD, WinnerTakesAll) takes that path and leaves no cost volume."""
+    left, right, _ = synth.random_dot_pair(H, W, D, seed=5 * H + W, scale=scale)
+    l, r = cuda(left), cuda(right)
+    ssd = sm.cost.SSD(D, k)
+    want = sm.disparity_reduce.WinnerTakesAll()(ssd(l, r))
+    got = ssd.cost_and_reduce(l, r)
+    assert got is not None and got.dtype == torch.int32
+    assert torch.equal(got, want)
+    assert torch.equal(ssd.cost_and_reduce(l, r, got), want)  # second call: the scratch keys are re-initialised
+    if H * W * D < 12_000_000:
+        assert np.array_equal(got.cpu().numpy(), O.wta(O.ssd(left, right, D, k)))
+    pipe = sm.Pipeline(sm.cost.SSD(D, k), sm.disparity_reduce.WinnerTakesAll())
+    assert torch.equal(pipe.estimate(l, r), want) and pipe._cost_volume is None
+    pipe.fuse_cost_and_reduce = False
+    assert torch.equal(pipe.estimate(l, r), want) and pipe._cost_volume is not None
+    # ties: constant images make every cost 0 -> lowest d wins everywhere (also across CTA chunks)
+    z = torch.full((H, W), 7.0, device="cuda")
+    assert int(ssd.cost_and_reduce(z, z).max()) == 0
+    # NaN at d = 0 -> 0 (the reference's `<` never replaces a NaN best); a NaN elsewhere never wins
+    ln = l.clone()
+    ln[H // 2, W // 2] = float("nan")
+    assert torch.equal(ssd.cost_and_reduce(ln, r), sm.disparity_reduce.WinnerTakesAll()(ssd(ln, r)))
+
+
+def test_ssd_with_winner_takes_all_unsupported_shapes_fall_back(sm):
+    left, right, _ = synth.random_dot_pair(24, 60, 32, seed=9, scale="raw")
+    l, r = cuda(left), cuda(right)
+    wta = sm.disparity_reduce.WinnerTakesAll()
+    assert sm.cost.SSD(30).cost_and_reduce(l, r) is None          # D % 4 != 0
+    assert sm.cost.SSD(32, 5).cost_and_reduce(l, r) is None       # window the packed kernel is not built for
+    for cost in (sm.cost.SSD(30), sm.cost.SSD(32, 5)):
+        pipe = sm.Pipeline(cost, wta)
+        assert torch.equal(pipe.estimate(l, r), wta(cost(l, r)))
+
+
 def test_dp_default_mode_stays_close_to_the_pinned_cpu_exact_mode(sm):
     """The default (Jacobi) DP mode is a defined variant, not the reference CPU functor: they are
     different algorithms (SURVEY.md 8.1 measured 4.56 % of pixels different at 375x450x64).  The

@@ -1,5 +1,5 @@
 """Per-stage device times (CUDA events, L2-exceeding volumes) -- developer tool.
-    python tools/stage_bench.py [H W D] [--stages ssd,bt,sgm,wta,dp,sgm_wta] [--reps N]
+    python tools/stage_bench.py [H W D] [--stages ssd,bt,sgm,wta,dp,sgm_wta,ssd_wta,bt_wta] [--reps N]
 sgm_wta = aggregation with the argmin folded in and no volume stored: what Pipeline.estimate runs."""
 import argparse
 import json
@@ -29,7 +29,8 @@ try:
 except Exception:
     peak = 6573.2
 algo = {"ssd": 4 * N + 8 * H * W, "bt": 4 * N + 8 * H * W, "sgm": 8 * N + 4 * H * W,
-        "wta": 4 * N + 4 * H * W, "dp": 5 * N + 5 * H * W + 8 * H * D, "sgm_wta": 4 * N + 8 * H * W}
+        "wta": 4 * N + 4 * H * W, "dp": 5 * N + 5 * H * W + 8 * H * D, "sgm_wta": 4 * N + 8 * H * W,
+        "ssd_wta": 28 * H * W, "bt_wta": 12 * H * W}
 ssd, bt = stereomatch.cost.SSD(D), stereomatch.cost.Birchfield(D)
 sgm, wta = stereomatch.aggregation.Semiglobal(), stereomatch.disparity_reduce.WinnerTakesAll()
 dp = stereomatch.disparity_reduce.DynamicProgramming()
@@ -38,7 +39,8 @@ agg = torch.empty_like(cost)
 disp = torch.empty(H, W, dtype=torch.int32, device="cuda")
 fns = {"ssd": lambda: ssd(l, r, cost), "bt": lambda: bt(l, r, agg), "sgm": lambda: sgm(cost, l, agg),
        "wta": lambda: wta(agg, disp), "dp": lambda: dp(cost, disp),
-       "sgm_wta": lambda: sgm.aggregate_and_reduce(cost, l, agg, disp, keep_volume=False)}
+       "sgm_wta": lambda: sgm.aggregate_and_reduce(cost, l, agg, disp, keep_volume=False),
+       "ssd_wta": lambda: ssd.cost_and_reduce(l, r, disp), "bt_wta": lambda: bt.cost_and_reduce(l, r, disp)}
 res = {}
 for name in a.stages.split(","):
     fn = fns[name]
