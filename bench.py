@@ -334,6 +334,9 @@ def run_b200_arm(args):
     stages = {k: stage_record(v, ALGO_BYTES[k], N) for k, v in stage_t.items()}
     stages["sgm_wta_fused_call"] = {"ms": round(ms_fused, 4),
                                     "note": "stm_sgm_wta_f32 + STM_SGM_DISPARITY_ONLY, what Pipeline.estimate runs"}
+    ms_single = stage_ms(lambda: pipe.estimate(l, r))
+    stages["frame_single"] = {"ms": round(ms_single, 4), "Gpix_disp_s": round(N / (ms_single * 1e-3) / 1e9, 2),
+                              "note": "Pipeline.estimate, ONE frame in flight, device-resident (latency of a frame)"}
 
     passes = []
     fused = len(pass_ms) == 4  # horizontal passes + two fused vertical sweeps (sgm_vsweep.cu)
@@ -411,10 +414,11 @@ def run_b200_arm(args):
         rec["stages"]["wta"] = stage_record(stage_ms(lambda: wt(cvol, dimg)), 4.0 + 4.0 / Dc, n_pd)
         p_ = stereomatch.Pipeline(cost_op, wt)
         p_._disparity_image = dimg
+        p_.fuse_cost_and_reduce = "always"   # Pipeline's own rule folds above 48 MB only (L2-resident volumes lose)
         fused = stage_ms(lambda: p_.estimate(lc, rc))
         rec["frame"] = {"ms": round(fused, 4), "Gpix_disp_s": round(n_pd / (fused * 1e-3) / 1e9, 2),
                         "hbm_bytes_per_pixel": 28,
-                        "note": "Pipeline.estimate = one pass, no volume (stm_ssd_wta_f32); device-resident"}
+                        "note": "one pass, no volume (stm_ssd_wta_f32); Pipeline.estimate's default above 48 MB; device-resident"}
         p_.fuse_cost_and_reduce = False
         p_._cost_volume = cvol
         two = stage_ms(lambda: p_.estimate(lc, rc))

@@ -49,6 +49,16 @@ class Pipeline:
         # `_aggregation_volume` after estimate().
         self.keep_aggregation_volume = False
 
+    def _fold_pays(self, left_image: torch.Tensor) -> bool:
+        """Birchfield + WTA in one kernel wins at every size.  SSD + WTA pays for its atomics and
+        shuffles: a win when the volume would go through HBM (1080p D=128: 0.45 -> 0.42 ms, and no
+        1 GB volume), a loss while the volume stays in L2 (450x375 D=64: 0.057 -> 0.070 ms), so the
+        fold is used above 48 MB -- the threshold of the other size rules (aggregation.py).
+        fuse_cost_and_reduce = "always" forces it."""
+        if type(self.cost) is not SSD or self.fuse_cost_and_reduce == "always":
+            return True
+        return left_image.numel() * self.cost.max_disparity * 4 > (48 << 20)
+
     def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor,
                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """[H,W] left/right images (CUDA float32) -> int32 [H,W] disparity map.
@@ -64,7 +74,8 @@ class Pipeline:
             finally:
                 self._disparity_image = keep
         if (self.fuse_cost_and_reduce and self.aggregation is None and type(self.cost) in (Birchfield, SSD)
-                and type(self.disparity_reduce) is WinnerTakesAll):
+                and type(self.disparity_reduce) is WinnerTakesAll
+                and self._fold_pays(left_image)):
             # cost + reduce in one pass, the volume never materialised (stm_birchfield_wta_f32,
             # stm_ssd_wta_f32)
             fused = self.cost.cost_and_reduce(left_image, right_image, self._disparity_image)

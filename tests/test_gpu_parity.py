@@ -632,6 +632,10 @@ def test_ssd_with_winner_takes_all_folded_in(sm, H, W, D, k, scale):
     if H * W * D < 12_000_000:
         assert np.array_equal(got.cpu().numpy(), O.wta(O.ssd(left, right, D, k)))
     pipe = sm.Pipeline(sm.cost.SSD(D, k), sm.disparity_reduce.WinnerTakesAll())
+    big = H * W * D * 4 > (48 << 20)   # below 48 MB the volume stays in L2 and the two stages are faster
+    assert torch.equal(pipe.estimate(l, r), want) and (pipe._cost_volume is None) == big
+    pipe = sm.Pipeline(sm.cost.SSD(D, k), sm.disparity_reduce.WinnerTakesAll())
+    pipe.fuse_cost_and_reduce = "always"
     assert torch.equal(pipe.estimate(l, r), want) and pipe._cost_volume is None
     pipe.fuse_cost_and_reduce = False
     assert torch.equal(pipe.estimate(l, r), want) and pipe._cost_volume is not None
