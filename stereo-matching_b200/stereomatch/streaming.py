@@ -12,6 +12,9 @@ downloads one frame after the other on the default stream).  Two helpers, both r
   download of earlier ones run on their own streams while the compute streams work; inputs and
   results are buffered on the device, so nothing is allocated per frame.
 
+* `GraphedPipeline` -- one `Pipeline.estimate` of a fixed shape captured into a CUDA graph: a small
+  frame costs the host ~25 driver calls (0.116 ms at 450x375 D=64), the replay is one (0.035 ms).
+
 Every pipeline owns its volumes (2 x 1.06 GB at 1080p D=128), so a second one doubles that.
 Work is ordered after the caller's current stream, and on return that stream has been made to
 wait for everything issued here.
@@ -70,6 +73,59 @@ class BatchEstimator:
                 done.record(s)
                 main.wait_event(done)
         return results
+
+
+class GraphedPipeline:
+    """`Pipeline.estimate` for ONE image shape, captured once into a CUDA graph and replayed.
+
+    What it buys is HOST time.  At 450x375 D=64 (the size the reference's own tests and benchmarks
+    use) `estimate` is ~25 driver calls -- the cost kernel, eight aggregation directions on helper
+    streams with their fork / join events, the sum, the argmin -- and costs the calling thread
+    0.116 ms per frame; the replay is one call, 0.035 ms (measured, tools/graph_probe.py).  The
+    device time of the frame does not change (0.32 ms: the GPU, not the host, is the longer side
+    even at this size), so this is for callers whose host thread has other work, or who drive
+    several small pipelines from one thread.  At 1080p it is correct and pointless.
+
+    The images are copied into buffers the graph owns (pass `self.left` / `self.right`, filled in
+    place, to skip the copies); the map is returned in `self.out` (or copied into `out`).  The
+    pipeline's volumes and the stream-keyed workspaces are allocated by two eager warm-up frames on
+    the capture stream and must not be used by anything else while the graph is alive.
+    """
+
+    def __init__(self, pipeline: Pipeline, height: int, width: int, device="cuda"):
+        if not isinstance(pipeline, Pipeline):
+            raise TypeError("expected a stereomatch.Pipeline")
+        self.pipeline = pipeline
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("GraphedPipeline: stereomatch_b200 is CUDA-only")
+        with torch.cuda.device(self.device):
+            self.left = torch.zeros(height, width, dtype=torch.float32, device=self.device)
+            self.right = torch.zeros(height, width, dtype=torch.float32, device=self.device)
+            self.out = torch.empty(height, width, dtype=torch.int32, device=self.device)
+            self._stream = torch.cuda.Stream(self.device)
+            self._stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self._stream):
+                for _ in range(2):  # allocations, per-device kernel attributes, lazy module loading
+                    pipeline.estimate(self.left, self.right, out=self.out)
+            self._stream.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph, stream=self._stream):
+                pipeline.estimate(self.left, self.right, out=self.out)
+
+    def estimate(self, left_image: torch.Tensor, right_image: torch.Tensor,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Same result as `pipeline.estimate(left_image, right_image)`; enqueued on the current stream."""
+        for src, dst in ((left_image, self.left), (right_image, self.right)):
+            if src is not dst:
+                if tuple(src.shape) != tuple(dst.shape):
+                    raise RuntimeError(f"GraphedPipeline: captured for {tuple(dst.shape)}, got {tuple(src.shape)}")
+                dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        if out is not None:
+            out.copy_(self.out, non_blocking=True)
+            return out
+        return self.out
 
 
 class HostFrameStreamer:

@@ -487,6 +487,36 @@ def test_host_frame_streamer_matches_per_frame_estimate(sm, extra):
         streamer.run([(cuda(frames[0][0]), cuda(frames[0][1]))], outs[:1])
 
 
+@pytest.mark.parametrize("kind,H,W,D", [("ssd_sgm_wta", 375, 450, 64), ("bt_sgm_wta", 120, 200, 64),
+                                         ("ssd_dp", 96, 160, 64), ("ssd_wta", 64, 96, 32),
+                                         ("ssd_sgm_wta", 1080, 1920, 128)])
+def test_graphed_pipeline_replays_exactly_what_estimate_computes(sm, kind, H, W, D):
+    """streaming.GraphedPipeline: Pipeline.estimate of one shape captured into a CUDA graph (helper
+    streams of the concurrent / overlapped SGM schedules and the cooperative sweeps included) and
+    replayed for new images returns exactly the eager result, frame after frame."""
+    def make():
+        cost = sm.cost.Birchfield(D) if kind.startswith("bt") else sm.cost.SSD(D)
+        if kind.endswith("dp"):
+            return sm.Pipeline(cost, sm.disparity_reduce.DynamicProgramming())
+        agg = sm.aggregation.Semiglobal() if "sgm" in kind else None
+        return sm.Pipeline(cost, sm.disparity_reduce.WinnerTakesAll(), agg)
+    frames = [synth.random_dot_pair(H, W, D, seed=900 + f, scale="raw")[:2] for f in range(3)]
+    dev = [(cuda(l), cuda(r)) for l, r in frames]
+    eager = make()
+    want = [eager.estimate(l, r).clone() for l, r in dev]
+    graphed = sm.streaming.GraphedPipeline(make(), H, W)
+    for _ in range(2):
+        for (l, r), w in zip(dev, want):
+            got = graphed.estimate(l, r)
+            assert got.data_ptr() == graphed.out.data_ptr() and torch.equal(got, w)
+    mine = torch.full((H, W), -1, dtype=torch.int32, device="cuda")
+    assert graphed.estimate(*dev[1], out=mine) is mine and torch.equal(mine, want[1])
+    graphed.left.copy_(dev[2][0]); graphed.right.copy_(dev[2][1])        # in-place inputs: no copies
+    assert torch.equal(graphed.estimate(graphed.left, graphed.right), want[2])
+    with pytest.raises(RuntimeError, match="captured for"):
+        graphed.estimate(dev[0][0][:-1], dev[0][1][:-1])
+
+
 def test_errors_mirror_the_reference(sm):
     img = torch.zeros(8, 8, device="cuda")
     with pytest.raises(RuntimeError, match="type not supported"):

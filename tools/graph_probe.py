@@ -58,4 +58,12 @@ for name, fn in (("sgm", lambda: sgm(cost, l, agg)),
     except Exception as e:  # capture may be refused by a call inside the library
         res[name]["graph_error"] = str(e)[:200]
         torch.cuda.synchronize()
+pipe = stereomatch.Pipeline(stereomatch.cost.SSD(D), stereomatch.disparity_reduce.WinnerTakesAll(),
+                            stereomatch.aggregation.Semiglobal())
+gp = stereomatch.streaming.GraphedPipeline(
+    stereomatch.Pipeline(stereomatch.cost.SSD(D), stereomatch.disparity_reduce.WinnerTakesAll(),
+                         stereomatch.aggregation.Semiglobal()), H, W)
+d1, h1 = timed(lambda: pipe.estimate(l, r))
+d2, h2 = timed(lambda: gp.estimate(l, r))
+res["frame"] = {"device_ms": d1, "host_enqueue_ms": h1, "graph_device_ms": d2, "graph_host_ms": h2}
 print(json.dumps(res))
