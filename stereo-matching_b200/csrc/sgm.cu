@@ -633,10 +633,21 @@ static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
 // those the eight directions run CONCURRENTLY on library-owned streams, each into its own
 // buffer, and one kernel then adds the buffers in the reference's order (corner-diagonal
 // replays included), so the result is bit-identical to the sequential passes.  It costs
-// 8 volume-sized buffers of workspace and ~25 % more traffic, hence only below 48 MB.
+// 8 volume-sized buffers of workspace and ~10 % more traffic.  Up to 48 MB the buffers are part of
+// the workspace every caller provides (stm_sgm_workspace_bytes).  MID-SIZE volumes (up to 384 MB)
+// that do not take the fused sweeps -- 375x450x128, the reference's own SGM benchmark shape; VGA;
+// 720p at D=64 -- are latency-bound as eight passes one after the other too (a pass is W or H
+// dependent steps of ~0.17 us, its bytes need less): they run concurrently when the caller provides
+// the buffers (stm_sgm_workspace_bytes_flags asks for them; measured 0.68 -> 0.45 ms at 375x450x128,
+// 0.83 -> 0.45 at 480x640x64, 1.54 -> 1.14 at 720x1280x64, 0.92 -> 0.76 at 480x640x128); above that
+// a pass is bound by its bytes and the sequential schedule moves fewer of them.
 constexpr size_t kConcurrentMaxVolumeBytes = (size_t)48 << 20;
+constexpr size_t kConcurrentMidVolumeBytes = (size_t)384 << 20;
 static bool sgm_concurrent_eligible(int H, int W, int D) {
   return H >= 2 && H <= W && (size_t)H * W * D * sizeof(float) <= kConcurrentMaxVolumeBytes;
+}
+static bool sgm_concurrent_mid_size(int H, int W, int D) {
+  return H >= 2 && H <= W && (size_t)H * W * D * sizeof(float) <= kConcurrentMidVolumeBytes;
 }
 static size_t sgm_base_workspace_bytes(int H, int W, int D) {
   const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_vsweep_workspace_bytes(H, W, D);
@@ -654,13 +665,20 @@ static bool sgm_four_stream_shape(int D);
 // with STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP: one more volume after the base workspace, and a
 // second one with STM_SGM_DISPARITY_ONLY (the four-stream schedule, see sgm_fused_overlap)
 size_t sgm_workspace_bytes_flags(int H, int W, int D, unsigned flags) {
-  const size_t plain = sgm_workspace_bytes(H, W, D);
-  if ((flags & (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP)) != (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP) ||
-      !sgm_overlap_shape(H, W, D))
-    return plain;
-  const size_t volumes = ((flags & STM_SGM_DISPARITY_ONLY) && sgm_four_stream_shape(D)) ? 2 : 1;
-  const size_t need = align256(sgm_base_workspace_bytes(H, W, D)) + volumes * H * W * D * sizeof(float);
-  return need > plain ? need : plain;
+  size_t need = sgm_workspace_bytes(H, W, D);
+  // mid-size volumes without the fused sweeps: the eight direction buffers of the concurrent schedule
+  const bool sweeps = (flags & STM_SGM_FUSED_SWEEPS) && sgm_vsweep_workspace_bytes(H, W, D) != 0;
+  if (!(flags & STM_SGM_SEQUENTIAL) && !sweeps && sgm_concurrent_mid_size(H, W, D)) {
+    const size_t c = align256(sgm_base_workspace_bytes(H, W, D)) + (size_t)8 * H * W * D * sizeof(float);
+    if (c > need) need = c;
+  }
+  if ((flags & (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP)) == (STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP) &&
+      sgm_overlap_shape(H, W, D)) {
+    const size_t volumes = ((flags & STM_SGM_DISPARITY_ONLY) && sgm_four_stream_shape(D)) ? 2 : 1;
+    const size_t o = align256(sgm_base_workspace_bytes(H, W, D)) + volumes * H * W * D * sizeof(float);
+    if (o > need) need = o;
+  }
+  return need;
 }
 
 // out = [out +] b0 + b1 + ... + b7, one fp32 addition at a time in the reference's order; the
@@ -966,8 +984,10 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   {
     static const char *off = getenv("STM_DEBUG_SGM_CONCURRENT");  // developer knob: "0" disables
     // (per-pass timing measures the sequential passes, so it selects them)
-    if (sgm_concurrent_eligible(H, W, D) && !(flags & STM_SGM_SEQUENTIAL) && !g_pass_timing &&
-        !(off && off[0] == '0')) {
+    const size_t with_buffers = align256(sgm_base_workspace_bytes(H, W, D)) + (size_t)8 * H * W * D * sizeof(float);
+    const bool buffers = sgm_concurrent_eligible(H, W, D) ||
+                         (sgm_concurrent_mid_size(H, W, D) && workspace != nullptr && workspace_bytes >= with_buffers);
+    if (buffers && !(flags & STM_SGM_SEQUENTIAL) && !g_pass_timing && !(off && off[0] == '0')) {
       float *bufs = reinterpret_cast<float *>(static_cast<char *>(workspace) +
                                               align256(sgm_base_workspace_bytes(H, W, D)));
 #define STM_SGM_CC(NV_, VW_)          \

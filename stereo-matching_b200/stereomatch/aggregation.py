@@ -21,10 +21,12 @@ class Semiglobal:
     Three schedules, same per-direction values:
       * one kernel per direction, the eight directions added into the output in the reference's
         order (bit-identical to the compiled CPU reference for W >= H);
-      * concurrent_directions=True (default): small landscape / square volumes (<= 48 MB,
-        latency-bound) run the eight directions at the same time into per-direction buffers that
-        are then added in the reference's order -- bit-identical to the sequential passes,
-        which concurrent_directions=False forces;
+      * concurrent_directions=True (default): landscape / square volumes that are latency-bound
+        one pass after the other (<= 48 MB always; up to 384 MB when the fused sweeps do not
+        apply, e.g. 375x450x128, VGA, 720p at D=64) run the eight directions at the same time
+        into per-direction buffers that are then added in the reference's order -- bit-identical
+        to the sequential passes, which concurrent_directions=False forces.  Costs eight
+        volume-sized buffers of workspace;
       * fused_sweeps: the two horizontal passes, then the six directions with a vertical
         component as two fused sweeps (csrc/sgm_vsweep.cu): four passes over the volumes instead
         of eight.  The sum is associated per sweep (0, 1, 2+4+6, 3+5+7) -- within 1e-4 of the

@@ -58,7 +58,7 @@ def test_workspace_query_is_pure():
     a256 = lambda n: (n + 255) // 256 * 256
     for H, W, D, dpad in ((375, 450, 64, 64), (20, 30, 32, 32), (64, 64, 128, 128)):
         assert lib.stm_sgm_workspace_bytes(H, W, D) == a256(expect(H, W, dpad)) + 8 * H * W * D * 4
-    assert lib.stm_sgm_workspace_bytes(480, 640, 128) == expect(480, 640, 128)   # 157 MB: sequential
+    assert lib.stm_sgm_workspace_bytes(480, 640, 128) == expect(480, 640, 128)   # 157 MB: the minimum is sequential
     # the overlapped schedule (STM_SGM_FUSED_SWEEPS 4 | STM_SGM_OVERLAP 32): one more volume after the
     # base workspace, two with STM_SGM_DISPARITY_ONLY (8) at 128 padded disparities; none at D > 128
     lib.stm_sgm_workspace_bytes_flags.restype = ctypes.c_size_t
@@ -67,6 +67,16 @@ def test_workspace_query_is_pure():
                                     (192, 192, 44, 0), (128, 128, 4, 0), (128, 128, 32, 0)):
         want = expect(H, W, dpad) if volumes == 0 else a256(expect(H, W, dpad)) + volumes * H * W * D * 4
         assert lib.stm_sgm_workspace_bytes_flags(H, W, D, flags) == want, (D, flags)
+    # mid-size volumes (48..384 MB) that do not take the fused sweeps: the flags query asks for the eight
+    # direction buffers of the concurrent schedule; not with STM_SGM_SEQUENTIAL (16), not when the sweeps run
+    for H, W, D in ((375, 450, 128), (480, 640, 64), (720, 1280, 64)):
+        base = expect(H, W, D)
+        assert lib.stm_sgm_workspace_bytes(H, W, D) == base
+        assert lib.stm_sgm_workspace_bytes_flags(H, W, D, 1) == a256(base) + 8 * H * W * D * 4
+        assert lib.stm_sgm_workspace_bytes_flags(H, W, D, 1 | 16) == base
+        assert lib.stm_sgm_workspace_bytes_flags(H, W, D, 1 | 4) == base
+    assert lib.stm_sgm_workspace_bytes_flags(540, 960, 96, 1 | 4) == a256(expect(540, 960, 96)) + 8 * 540 * 960 * 96 * 4
+    assert lib.stm_sgm_workspace_bytes_flags(1080, 1920, 64, 1) == expect(1080, 1920, 64)   # 531 MB: sequential
 
 
 def test_python_api_surface_matches_reference():

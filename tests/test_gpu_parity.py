@@ -203,7 +203,9 @@ def test_sgm_accumulates_like_the_reference(sm):
     assert_volume_close(out, want)
 
 
-@pytest.mark.parametrize("H,W,D", [(20, 33, 32), (24, 24, 64), (17, 60, 128), (13, 35, 192), (11, 29, 20)])
+@pytest.mark.parametrize("H,W,D", [(20, 33, 32), (24, 24, 64), (17, 60, 128), (13, 35, 192), (11, 29, 20),
+                                   (375, 450, 128),    # 86 MB: the reference's own SGM benchmark shape
+                                   (480, 640, 64)])    # 79 MB, VGA: mid-size volumes, workspace from the flags query
 def test_sgm_concurrent_directions_equal_the_sequential_passes(sm, H, W, D):
     """Small landscape / square volumes run the eight directions concurrently into separate
     buffers and add them in the reference's order: bit-identical to the sequential passes
