@@ -136,14 +136,14 @@ int stm_ssd_wta_f32(const float *left, const float *right, int32_t *disparity, i
  * and ACCUMULATES into `out` unless STM_SGM_OVERWRITE.  `workspace` must hold
  * stm_sgm_workspace_bytes(H, W, D) bytes of device memory (may be NULL if that is 0): one
  * path's worth of vectors for the corner-diagonal replay, the CTA-to-CTA rings and the per-pixel
- * penalties of the fused sweeps and, for landscape / square volumes of at most 48 MB, eight
+ * penalties of the fused sweeps and, for volumes of at most 48 MB, eight
  * volume-sized buffers (those
  * shapes run the eight directions concurrently on library-owned streams that are forked from and
  * joined to `stream`; see STM_SGM_SEQUENTIAL).  The query is a pure function of the shape. */
 size_t stm_sgm_workspace_bytes(int H, int W, int D);
 /* The same query for calls that pass `flags`: what the FASTEST schedule for those flags wants.  More than
  * stm_sgm_workspace_bytes in two cases: STM_SGM_FUSED_SWEEPS | STM_SGM_OVERLAP asks for one more volume (two
- * with STM_SGM_DISPARITY_ONLY at D = 128); and a landscape / square volume of 48 to 384 MB that does not take
+ * with STM_SGM_DISPARITY_ONLY at D = 128); and a volume of 48 to 384 MB that does not take
  * the fused sweeps (no STM_SGM_FUSED_SWEEPS, or a D they do not handle) asks for the eight direction buffers of
  * the concurrent schedule -- such volumes are latency-bound one pass after the other (375x450x128: 0.68 ->
  * 0.45 ms).  A workspace of only stm_sgm_workspace_bytes is always accepted; the call then runs the passes

@@ -643,11 +643,13 @@ static size_t sgm_direction_workspace_bytes(int H, int W, int D) {
 // a pass is bound by its bytes and the sequential schedule moves fewer of them.
 constexpr size_t kConcurrentMaxVolumeBytes = (size_t)48 << 20;
 constexpr size_t kConcurrentMidVolumeBytes = (size_t)384 << 20;
+// (portrait images too since r02 v12: the sum kernel takes the multiplicities per pixel and puts the
+// corner diagonal's extra runs where the reference's list order puts them for H > W)
 static bool sgm_concurrent_eligible(int H, int W, int D) {
-  return H >= 2 && H <= W && (size_t)H * W * D * sizeof(float) <= kConcurrentMaxVolumeBytes;
+  return H >= 2 && W >= 2 && (size_t)H * W * D * sizeof(float) <= kConcurrentMaxVolumeBytes;
 }
 static bool sgm_concurrent_mid_size(int H, int W, int D) {
-  return H >= 2 && H <= W && (size_t)H * W * D * sizeof(float) <= kConcurrentMidVolumeBytes;
+  return H >= 2 && W >= 2 && (size_t)H * W * D * sizeof(float) <= kConcurrentMidVolumeBytes;
 }
 static size_t sgm_base_workspace_bytes(int H, int W, int D) {
   const size_t a = sgm_direction_workspace_bytes(H, W, D), b = sgm_vsweep_workspace_bytes(H, W, D);
@@ -681,20 +683,23 @@ size_t sgm_workspace_bytes_flags(int H, int W, int D, unsigned flags) {
   return need;
 }
 
-// out = [out +] b0 + b1 + ... + b7, one fp32 addition at a time in the reference's order; the
-// corner up-diagonals (x - y == W - H for direction 5, x + y == H - 1 for direction 7) get
-// their vector `times` more times right after that direction, as the sequential path does.
+// out = [out +] b0 + b1 + ... + b7, one fp32 addition at a time in the reference's order.  The
+// corner up-diagonals (multiplicity m > 1: direction 5 where x - y == W - H, direction 7 where
+// x + y == H - 1 on landscape images) get their vector m - 1 more times where the sequential
+// schedules put them: right after that direction on landscape images (sgm_by_direction), BEFORE
+// direction 4 on portrait ones (sgm_by_direction_portrait; the defective descriptors precede the
+// corner diagonal's own in the reference's list).  Pixels a defective direction never visits hold 0
+// in its buffer (memset by the caller).
 template <int VEC>
 __global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict__ bufs,
-                                size_t n_vec, size_t stride, int H, int W, int D, int accumulate,
-                                int times) {
+                                size_t n_vec, size_t stride, int H, int W, int D, int accumulate) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_vec) return;
   const size_t e = i * VEC;           // first element of this thread
   const size_t pixel = e / D;
   const int x = (int)(pixel % W), y = (int)(pixel / W);
-  const bool corner5 = times > 0 && x - y == W - H;
-  const bool corner7 = times > 0 && x + y == H - 1;
+  const int extra5 = max(sgm_mult5(x, y, H, W) - 1, 0), extra7 = max(sgm_mult7(x, y, H, W) - 1, 0);
+  const bool portrait = H > W;
   float s[VEC], b[VEC];
   auto load = [&](const float *p) {
     if constexpr (VEC == 4) {
@@ -703,6 +708,11 @@ __global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict
     } else {
       b[0] = p[e];
     }
+  };
+  auto add_b = [&](int times) {
+    for (int r = 0; r < times; ++r)
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) s[k] = __fadd_rn(s[k], b[k]);
   };
   load(bufs);
   if (accumulate) {
@@ -716,13 +726,14 @@ __global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict
     for (int k = 0; k < VEC; ++k) s[k] = b[k];
   }
   for (int dir = 1; dir < 8; ++dir) {
+    if (dir == 4 && portrait && extra5 > 0) {
+      load(bufs + (size_t)5 * stride);
+      add_b(extra5);
+    }
     load(bufs + (size_t)dir * stride);
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) s[k] = __fadd_rn(s[k], b[k]);
-    if ((dir == 5 && corner5) || (dir == 7 && corner7))
-      for (int r = 0; r < times; ++r)
-#pragma unroll
-        for (int k = 0; k < VEC; ++k) s[k] = __fadd_rn(s[k], b[k]);
+    add_b(1);
+    if (dir == 5 && !portrait) add_b(extra5);
+    if (dir == 7) add_b(extra7);
   }
   if constexpr (VEC == 4) {
     *reinterpret_cast<float4 *>(out + e) = make_float4(s[0], s[1], s[2], s[3]);
@@ -912,8 +923,9 @@ static int sgm_concurrent(const float *cost, const float *image, float *out, int
     float *b = bufs + (size_t)dir * N;
     if (dir > 0 && cudaStreamWaitEvent(s, aux->fork, 0) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: cudaStreamWaitEvent failed");
-    // the defective up-diagonals skip a band of a landscape image: those pixels contribute 0
-    if ((dir == 5 || dir == 7) && W > H &&
+    // the defective up-diagonals skip a band of the image (direction 5 whenever W != H, direction 7
+    // on landscape images): those pixels contribute 0
+    if (((dir == 5 && W != H) || (dir == 7 && W > H)) &&
         cudaMemsetAsync(b, 0, N * sizeof(float), s) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: cudaMemsetAsync failed");
     rc = run_direction<NV, VW>(cost, image, b, H, W, D, p1, p2, dir, 0, sgm_num_paths(dir, H, W),
@@ -925,15 +937,14 @@ static int sgm_concurrent(const float *cost, const float *image, float *out, int
         return fail(STM_ECUDA, "sgm: stream join failed");
     }
   }
-  const int times = W - H;  // extra runs of the corner diagonals (0 on square images)
   const int accumulate = (flags & STM_SGM_OVERWRITE) ? 0 : 1;
   if (D % 4 == 0) {
     const size_t n_vec = N / 4;
     sgm_sum8_kernel<4><<<(unsigned)((n_vec + 255) / 256), 256, 0, stream>>>(out, bufs, n_vec, N, H, W,
-                                                                          D, accumulate, times);
+                                                                          D, accumulate);
   } else {
     sgm_sum8_kernel<1><<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(out, bufs, N, N, H, W, D,
-                                                                      accumulate, times);
+                                                                      accumulate);
   }
   rc = check_launch("sgm_sum8_kernel");
   if (rc) return rc;
@@ -969,14 +980,14 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
 #define STM_SGM_FO(NV_, VW_)        \
   if (m.NV == NV_ && m.VW == VW_)   \
     rc = sgm_fused_overlap<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, workspace, workspace_bytes, stream, disp);
-      STM_SGM_FO(1, 4) STM_SGM_FO(1, 2) STM_SGM_FO(3, 2) STM_SGM_FO(1, 1)
+      STM_SGM_FO(1, 4) STM_SGM_FO(1, 2) STM_SGM_FO(3, 2) STM_SGM_FO(1, 1) STM_SGM_FO(3, 1) STM_SGM_FO(5, 1)
 #undef STM_SGM_FO
       if (rc != 1) return rc;
     }
 #define STM_SGM_FS(NV_, VW_)        \
   if (m.NV == NV_ && m.VW == VW_)   \
     rc = sgm_fused<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, workspace, workspace_bytes, stream, disp);
-    STM_SGM_FS(1, 4) STM_SGM_FS(2, 4) STM_SGM_FS(1, 2) STM_SGM_FS(3, 2) STM_SGM_FS(1, 1)
+    STM_SGM_FS(1, 4) STM_SGM_FS(2, 4) STM_SGM_FS(1, 2) STM_SGM_FS(3, 2) STM_SGM_FS(1, 1) STM_SGM_FS(3, 1) STM_SGM_FS(5, 1)
 #undef STM_SGM_FS
     if (rc != 1) return rc;
   }

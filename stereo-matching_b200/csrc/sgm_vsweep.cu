@@ -967,7 +967,9 @@ extern "C" __attribute__((visibility("default"))) int stm_debug_vsweep_stats(uns
 
 static bool vsweep_lane_map(int D) {
   const LaneMap m = pick_lane_map(D);
-  return (m.VW == 4 && m.NV <= 2) || (m.VW == 2 && (m.NV == 1 || m.NV == 3)) || (m.VW == 1 && m.NV == 1);
+  // VW == 1: D <= 32, and 64 < D <= 96 / 128 < D <= 160 (D = 96 and 160 are common search ranges)
+  return (m.VW == 4 && m.NV <= 2) || (m.VW == 2 && (m.NV == 1 || m.NV == 3)) ||
+         (m.VW == 1 && (m.NV == 1 || m.NV == 3 || m.NV == 5));
 }
 
 // [imported-row counters][CTA->CTA rings][penalties of both sweeps]
@@ -999,7 +1001,7 @@ bool sgm_vsweep_can_run(int H, int W, int D, int variant_group) {
 #define STM_VSWEEP_CASE(NV_, VW_) \
   if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W, variant_group, &minb) > 0;
   STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
-  STM_VSWEEP_CASE(1, 1)
+  STM_VSWEEP_CASE(1, 1) STM_VSWEEP_CASE(3, 1) STM_VSWEEP_CASE(5, 1)
 #undef STM_VSWEEP_CASE
   return false;
 }
@@ -1027,7 +1029,7 @@ int launch_sgm_vsweep(const float *cost, const float *image, float *out, const f
     return vsweep::run<NV_, VW_>(cost, image, out, extra, extra2, disp, H, W, D, p1, p2, min_limit, up, store_vol, \
                                  volume_streams, ws, stream);
   STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
-  STM_VSWEEP_CASE(1, 1)
+  STM_VSWEEP_CASE(1, 1) STM_VSWEEP_CASE(3, 1) STM_VSWEEP_CASE(5, 1)
 #undef STM_VSWEEP_CASE
   return 1;
 }

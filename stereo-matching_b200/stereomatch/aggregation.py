@@ -21,7 +21,7 @@ class Semiglobal:
     Three schedules, same per-direction values:
       * one kernel per direction, the eight directions added into the output in the reference's
         order (bit-identical to the compiled CPU reference for W >= H);
-      * concurrent_directions=True (default): landscape / square volumes that are latency-bound
+      * concurrent_directions=True (default): volumes that are latency-bound
         one pass after the other (<= 48 MB always; up to 384 MB when the fused sweeps do not
         apply, e.g. 375x450x128, VGA, 720p at D=64) run the eight directions at the same time
         into per-direction buffers that are then added in the reference's order -- bit-identical
@@ -33,8 +33,8 @@ class Semiglobal:
         reference order (measured 1.3e-5 at 1080p), not bit-identical.  fused_sweeps=None
         (default) uses them for volumes above 48 MB whose rows hold at least 704*128 values
         (where they are faster), True always, False never (reference order).
-        Shapes the sweeps do not handle (more than 13 columns per SM, D not in {<=32, 64, 128,
-        192, 256}) take the per-direction passes.
+        Shapes the sweeps do not handle (more than 13 columns per SM -- 26 at D <= 64 --, D not
+        in {<= 32, 64, 65..96, 128, 129..160, 192, 256}) take the per-direction passes.
       * overlap (with the fused sweeps; default on): the two horizontal passes run on a helper
         stream next to the down sweep, which writes a workspace volume of its own that the up
         sweep adds (STM_SGM_OVERLAP).  Costs one more volume of workspace (1.06 GB at 1080p

@@ -47,16 +47,17 @@ def test_workspace_query_is_pure():
         direction = min(H, W) * dpad * 4
         # + the adaptive penalties of both sweeps, one float4 per pixel each
         sweeps = (40960 + 320 * 16 * 3 * dpad * 8 + 2 * H * W * 16
-                  if (H >= 2 and W >= 2 and dpad in (32, 64, 128, 192, 256)) else 0)
+                  if (H >= 2 and W >= 2 and dpad in (32, 64, 96, 128, 160, 192, 256)) else 0)
         return max(direction, sweeps)
 
     assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == expect(1080, 1920, 128)
-    assert lib.stm_sgm_workspace_bytes(30, 18, 16) == expect(30, 18, 32)  # D=16 pads to 32 lanes
+    assert lib.stm_sgm_workspace_bytes(1920, 1080, 128) == expect(1920, 1080, 128)  # portrait
     assert lib.stm_sgm_workspace_bytes(0, 0, 0) == 0
-    # landscape / square volumes up to 48 MB also get one buffer per direction (csrc/sgm.cu,
+    # volumes up to 48 MB also get one buffer per direction (csrc/sgm.cu,
     # concurrent directions), after the base workspace rounded up to 256 bytes
     a256 = lambda n: (n + 255) // 256 * 256
-    for H, W, D, dpad in ((375, 450, 64, 64), (20, 30, 32, 32), (64, 64, 128, 128)):
+    for H, W, D, dpad in ((375, 450, 64, 64), (20, 30, 32, 32), (64, 64, 128, 128), (450, 375, 64, 64),
+                          (30, 18, 16, 32)):   # portrait too; D=16 pads to 32 lanes
         assert lib.stm_sgm_workspace_bytes(H, W, D) == a256(expect(H, W, dpad)) + 8 * H * W * D * 4
     assert lib.stm_sgm_workspace_bytes(480, 640, 128) == expect(480, 640, 128)   # 157 MB: the minimum is sequential
     # the overlapped schedule (STM_SGM_FUSED_SWEEPS 4 | STM_SGM_OVERLAP 32): one more volume after the
@@ -75,7 +76,9 @@ def test_workspace_query_is_pure():
         assert lib.stm_sgm_workspace_bytes_flags(H, W, D, 1) == a256(base) + 8 * H * W * D * 4
         assert lib.stm_sgm_workspace_bytes_flags(H, W, D, 1 | 16) == base
         assert lib.stm_sgm_workspace_bytes_flags(H, W, D, 1 | 4) == base
-    assert lib.stm_sgm_workspace_bytes_flags(540, 960, 96, 1 | 4) == a256(expect(540, 960, 96)) + 8 * 540 * 960 * 96 * 4
+    # D = 224 is not a lane map of the sweeps: the flag does not change what the call needs
+    assert lib.stm_sgm_workspace_bytes_flags(400, 900, 224, 1 | 4) == a256(expect(400, 900, 224)) + 8 * 400 * 900 * 224 * 4
+    assert lib.stm_sgm_workspace_bytes_flags(540, 960, 96, 1 | 4) == expect(540, 960, 96)   # D = 96: the sweeps run
     assert lib.stm_sgm_workspace_bytes_flags(1080, 1920, 64, 1) == expect(1080, 1920, 64)   # 531 MB: sequential
 
 

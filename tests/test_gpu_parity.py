@@ -157,7 +157,10 @@ def test_sgm_horizontal_bulk_copy_kernel_tiles(sm, H, W, D):
 @pytest.mark.parametrize("H,W,D", [(70, 150, 128), (150, 70, 64), (45, 333, 192), (33, 100, 32),
                                      (64, 64, 128), (5, 700, 64), (130, 9, 16), (24, 1900, 64),
                                      (40, 1920, 128), (37, 301, 256), (3, 2, 32), (2, 5, 64),
-                                     (20, 3840, 64), (9, 2500, 32), (7, 3848, 48), (6, 3850, 64)])
+                                     (20, 3840, 64), (9, 2500, 32), (7, 3848, 48), (6, 3850, 64),
+                                     # D = 96 / 160 and ranges below them (three / five scalar vectors per lane)
+                                     (60, 200, 96), (150, 70, 96), (40, 1920, 96), (33, 100, 80), (45, 333, 160),
+                                     (20, 301, 150), (64, 64, 96)])
 def test_sgm_sweeps_many_ctas_and_ring_wraps(sm, H, W, D):
     """Fused vertical sweeps (csrc/sgm_vsweep.cu): one CTA to 148 CTAs, 2 to 13 column slots
     per CTA, more rows than every hand-off ring (4 rows in shared memory, 16 in global memory),
@@ -204,6 +207,8 @@ def test_sgm_accumulates_like_the_reference(sm):
 
 
 @pytest.mark.parametrize("H,W,D", [(20, 33, 32), (24, 24, 64), (17, 60, 128), (13, 35, 192), (11, 29, 20),
+                                   (33, 20, 32), (60, 17, 128), (35, 13, 192), (29, 11, 20),   # portrait
+                                   (450, 375, 64), (640, 480, 64),                            # portrait, 43 / 79 MB
                                    (375, 450, 128),    # 86 MB: the reference's own SGM benchmark shape
                                    (480, 640, 64)])    # 79 MB, VGA: mid-size volumes, workspace from the flags query
 def test_sgm_concurrent_directions_equal_the_sequential_passes(sm, H, W, D):
@@ -584,7 +589,8 @@ def test_full_size_1080p_properties(sm):
     assert bool(torch.equal(d1, d2)) and int(d1.min()) >= 0 and int(d1.max()) < D
 
 
-@pytest.mark.parametrize("H,W,D", [(30, 47, 128), (47, 30, 64), (21, 21, 32), (19, 333, 192)])
+@pytest.mark.parametrize("H,W,D", [(30, 47, 128), (47, 30, 64), (21, 21, 32), (19, 333, 192), (30, 47, 96),
+                                   (19, 333, 160), (25, 90, 70)])
 def test_sgm_fused_sweeps_fold_winner_takes_all(sm, H, W, D):
     """stm_sgm_wta_f32 with STM_SGM_FUSED_SWEEPS: the up sweep emits the disparity map; it is
     exactly WinnerTakesAll of the volume the same call returns, the volume meets the oracle
