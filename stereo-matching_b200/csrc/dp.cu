@@ -260,7 +260,7 @@ int launch_dp(const float *cost, int8_t *path, float *row_final, int32_t *disp, 
     dp_backtrack_kernel<<<(H + 63) / 64, 64, 0, stream>>>(path, row_final, disp, H, W, D);
     return check_launch("dp_backtrack_kernel");
   }
-  {  // D % 64 == 0: cost tiles through the bulk-copy engine, prefetched backtrack (dp_bulk.cu)
+  {  // D % 32 == 0: cost tiles through the bulk-copy engine, prefetched backtrack (dp_bulk.cu)
     const int rc = launch_dp_bulk(cost, path, row_final, disp, H, W, D, stream);
     if (rc != 1) return rc;
   }

@@ -72,7 +72,7 @@ dp_row_bulk_kernel(const float *__restrict__ cost, int8_t *__restrict__ path, fl
   using namespace dpb;
   using C = Cfg<NV, VW>;
   constexpr int D = C::kD, TILE = C::kTile, TF = C::kTileFloats;
-  static_assert(VW == 4 || VW == 2, "bulk DP kernel: D must be a multiple of 64");
+  static_assert(VW == 4 || VW == 2 || VW == 1, "lane maps of sgm_paths.cuh");  // VW == 1: D = 32 NV exactly (host)
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
   const int row = blockIdx.x * kWarps + wi;
@@ -128,7 +128,8 @@ dp_row_bulk_kernel(const float *__restrict__ cost, int8_t *__restrict__ path, fl
       }
       const int d0 = lv_d<NV, VW>(lane, k, 0);
       if constexpr (VW == 4) *reinterpret_cast<char4 *>(pp + d0) = make_char4(dirs[0], dirs[1], dirs[2], dirs[3]);
-      else *reinterpret_cast<char2 *>(pp + d0) = make_char2(dirs[0], dirs[1]);
+      else if constexpr (VW == 2) *reinterpret_cast<char2 *>(pp + d0) = make_char2(dirs[0], dirs[1]);
+      else pp[d0] = dirs[0];
     }
   };
 
@@ -148,7 +149,8 @@ dp_row_bulk_kernel(const float *__restrict__ cost, int8_t *__restrict__ path, fl
         for (int k = 0; k < NV; ++k) {
           const int d0 = lv_d<NV, VW>(lane, k, 0);
           if constexpr (VW == 4) *reinterpret_cast<char4 *>(prow_w + d0) = make_char4(0, 0, 0, 0);
-          else *reinterpret_cast<char2 *>(prow_w + d0) = make_char2(0, 0);
+          else if constexpr (VW == 2) *reinterpret_cast<char2 *>(prow_w + d0) = make_char2(0, 0);
+          else prow_w[d0] = 0;
         }
       } else {
         step(col, c);
@@ -266,7 +268,7 @@ static int run_dp_bulk(const float *cost, int8_t *path, float *row_final, int32_
 // Returns 0 on success, 1 if the shape is not handled here (the caller runs dp_row_kernel), < 0 on error.
 int launch_dp_bulk(const float *cost, int8_t *path, float *row_final, int32_t *disp, int H, int W, int D,
                    cudaStream_t stream) {
-  if (D % 64 != 0 || W < 2) return 1;
+  if (D % 32 != 0 || W < 2) return 1;   // whole lane vectors: the tiles are copied as they lie in memory
   if ((reinterpret_cast<uintptr_t>(cost) & 15) || (reinterpret_cast<uintptr_t>(path) & 15) ||
       (reinterpret_cast<uintptr_t>(row_final) & 15))
     return 1;
@@ -279,6 +281,7 @@ int launch_dp_bulk(const float *cost, int8_t *path, float *row_final, int32_t *d
   if (m.NV == NV_ && m.VW == VW_) return run_dp_bulk<NV_, VW_>(cost, path, row_final, disp, H, W, stream);
   STM_DPB_CASE(1, 4) STM_DPB_CASE(2, 4) STM_DPB_CASE(3, 4) STM_DPB_CASE(4, 4)
   STM_DPB_CASE(1, 2) STM_DPB_CASE(3, 2) STM_DPB_CASE(5, 2) STM_DPB_CASE(7, 2)
+  STM_DPB_CASE(1, 1) STM_DPB_CASE(3, 1) STM_DPB_CASE(5, 1) STM_DPB_CASE(7, 1)
 #undef STM_DPB_CASE
   return 1;
 }

@@ -317,6 +317,8 @@ def test_dp_cpu_exact_golden(sm, golden, case):
                                           # backtrack windows of 16 columns: edges, many windows
                                           (3, 16, 64, "rand"), (3, 17, 64, "rand"), (3, 18, 64, "rand"),
                                           (6, 700, 128, "rand"), (5, 333, 192, "rand"),
+                                          # one scalar per lane and vector (D % 32 == 0, not % 64): bulk kernel since r02 v12
+                                          (6, 700, 96, "rand"), (5, 333, 160, "ties"), (4, 50, 224, "rand"),
                                           (4, 90, 5, "rand"),    # D smaller than the window
                                           (3, 120, 256, "rand"), (4, 400, 32, "ties"),
                                           # more rows than the 24-column-prefetch variant keeps
