@@ -124,7 +124,7 @@ int stm_birchfield_wta_f32(const float *left, const float *right, int32_t *dispa
  * disparity chunk to `scratch` with a 64-bit atomic minimum instead; a second small kernel writes the
  * int32 map.  HBM traffic is 28 bytes per PIXEL instead of 8 bytes per pixel-disparity.
  * `scratch`: stm_ssd_wta_scratch_bytes(H, W) bytes of device memory (H*W 64-bit words; contents
- * irrelevant on entry, garbage on exit).  kernel_size 7 or 3 and D % 4 == 0 only; other shapes return
+ * irrelevant on entry, garbage on exit).  kernel_size 1..10 and D % 4 == 0 only; other shapes return
  * STM_EUNSUPPORTED (the binding then runs the two stages).  New, SURVEY.md 8(f) N1. */
 size_t stm_ssd_wta_scratch_bytes(int H, int W);
 int stm_ssd_wta_f32(const float *left, const float *right, int32_t *disparity, int H, int W, int D,

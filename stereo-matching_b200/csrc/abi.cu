@@ -134,7 +134,7 @@ int stm_ssd_wta_f32(const float *left, const float *right, int32_t *disparity, i
   rc = launch_ssd_wta(left, right, disparity, static_cast<unsigned long long *>(scratch), H, W, D, kernel_size,
                       (cudaStream_t)stream);
   if (rc == 1)
-    return fail(STM_EUNSUPPORTED, "ssd_wta: needs kernel_size 7 or 3 and D %% 4 == 0 (got k=%d D=%d); "
+    return fail(STM_EUNSUPPORTED, "ssd_wta: needs 1 <= kernel_size <= 10 and D %% 4 == 0 (got k=%d D=%d); "
                 "use stm_ssd_f32 + stm_wta_f32", kernel_size, D);
   return rc;
 }

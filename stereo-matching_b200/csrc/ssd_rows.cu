@@ -495,6 +495,29 @@ static int run_ssd_rows(const float *left, const float *right, float *cost, unsi
   return check_launch("ssd_rows_kernel");
 }
 
+// Window half-sizes 1..10 (windows of 2x2 .. 20x20; the reference's default is 7; 9 and 10 spill ~45 registers).  <K, RUNS, NH>: a tile
+// of RUNS * 2K columns, NH horizontal warps.  K >= 5: one streaming row-pair item per H warp (NH = K);
+// smaller windows have fewer row pairs per group than warps worth running, so their H warps take
+// (row pair, run) items.  Tile sizes keep the double-buffered hand-off tile within shared memory and
+// the vertical ring (8K registers) within the register cap of the CTA.
+template <bool WTA>
+static int dispatch_ssd_rows(const float *left, const float *right, float *cost, unsigned long long *keys, int H,
+                             int W, int D, int k, cudaStream_t stream) {
+  switch (k) {
+    case 1: return run_ssd_rows<1, 24, 8, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 2: return run_ssd_rows<2, 12, 8, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 3: return run_ssd_rows<3, 8, 8, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 4: return run_ssd_rows<4, 6, 8, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 5: return run_ssd_rows<5, 4, 5, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 6: return run_ssd_rows<6, 4, 6, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 7: return run_ssd_rows<7, 3, STM_SSD_NH7, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 8: return run_ssd_rows<8, 2, 8, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 9: return run_ssd_rows<9, 2, 9, WTA>(left, right, cost, keys, H, W, D, stream);
+    case 10: return run_ssd_rows<10, 1, 10, WTA>(left, right, cost, keys, H, W, D, stream);
+    default: return 1;
+  }
+}
+
 // Returns 0 on success, 1 when the shape is not handled here (the caller runs ssd_tiled_kernel).
 int launch_ssd_rows(const float *left, const float *right, float *cost, int H, int W, int D, int k,
                     cudaStream_t stream) {
@@ -503,11 +526,7 @@ int launch_ssd_rows(const float *left, const float *right, float *cost, int H, i
     static const char *off = getenv("STM_DEBUG_SSD_ROWS");  // developer knob: "0" disables
     if (off && off[0] == '0') return 1;
   }
-  switch (k) {
-    case 7: return run_ssd_rows<7, 3, STM_SSD_NH7, false>(left, right, cost, nullptr, H, W, D, stream);
-    case 3: return run_ssd_rows<3, 8, 8, false>(left, right, cost, nullptr, H, W, D, stream);
-    default: return 1;
-  }
+  return dispatch_ssd_rows<false>(left, right, cost, nullptr, H, W, D, k, stream);
 }
 
 __global__ void ssd_wta_extract_kernel(const unsigned long long *__restrict__ keys, int32_t *__restrict__ disp, size_t n) {
@@ -516,14 +535,13 @@ __global__ void ssd_wta_extract_kernel(const unsigned long long *__restrict__ ke
 }
 
 // SSD cost + winner-takes-all without the volume (stm_ssd_wta_f32).  `keys` = H*W 64-bit words of scratch.
-// Returns 0 on success, 1 when the shape is not handled (k not 7 / 3, D % 4 != 0).
+// Returns 0 on success, 1 when the shape is not handled (k not in 1..10, D % 4 != 0).
 int launch_ssd_wta(const float *left, const float *right, int32_t *disp, unsigned long long *keys, int H, int W,
                    int D, int k, cudaStream_t stream) {
-  if (D % 4 != 0 || (k != 7 && k != 3)) return 1;
+  if (D % 4 != 0 || k < 1 || k > 10) return 1;
   const size_t n = (size_t)H * W;
   STM_CUDA_TRY(cudaMemsetAsync(keys, 0xff, n * sizeof(unsigned long long), stream));
-  const int rc = k == 7 ? run_ssd_rows<7, 3, STM_SSD_NH7, true>(left, right, nullptr, keys, H, W, D, stream)
-                        : run_ssd_rows<3, 8, 8, true>(left, right, nullptr, keys, H, W, D, stream);
+  const int rc = dispatch_ssd_rows<true>(left, right, nullptr, keys, H, W, D, k, stream);
   if (rc) return rc;
   ssd_wta_extract_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(keys, disp, n);
   return check_launch("ssd_wta_extract_kernel");

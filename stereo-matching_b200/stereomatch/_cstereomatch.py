@@ -302,7 +302,7 @@ class CostOps:
     def compute_ssd_wta(left_image, right_image, disparity_image, max_disparity: int, kernel_size: int) -> bool:
         """New: compute_ssd + run_winners_take_all in one pass, the volume never written
         (include/stm_abi.h, stm_ssd_wta_f32).  Returns False when the shape is not supported
-        (kernel_size not 7 / 3, D % 4 != 0): the caller then runs the two stages."""
+        (kernel_size not in 1..10, D % 4 != 0): the caller then runs the two stages."""
         left = _gpu("SSDKernel: left_image", left_image, torch.float32, 2)
         right = _gpu("SSDKernel: right_image", right_image, torch.float32, 2, left)
         disp = _out("disparity_image",

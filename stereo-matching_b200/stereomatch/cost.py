@@ -37,7 +37,7 @@ class SSD:
         """New: SSD cost followed by winner-takes-all in one pass; the cost volume is never written
         (28 bytes of HBM traffic per pixel instead of 8 per pixel-disparity).  Returns the int32
         disparity map -- exactly WinnerTakesAll()(self(left, right)) -- or None when the shape is
-        not supported (kernel_size not 7 / 3, max_disparity % 4 != 0), in which case the caller
+        not supported (kernel_size not in 1..10, max_disparity % 4 != 0), in which case the caller
         runs the two stages."""
         if self.cost_volume_dtype not in (torch.float, torch.float32):
             return None

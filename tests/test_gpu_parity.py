@@ -61,6 +61,14 @@ def test_ssd_golden(sm, golden, case):
     (37, 53, 32, 7, "raw"), (37, 53, 32, 7, "unit"), (19, 140, 64, 7, "unit"),
     (50, 31, 128, 7, "raw"), (23, 70, 192, 7, "unit"), (9, 11, 5, 2, "unit"),
     (16, 33, 32, 0, "raw"), (40, 200, 128, 7, "unit"),
+    # every window half-size the packed kernel is built for (1..10), tile edges in x, d and y;
+    # 11 and above take the straightforward kernel
+    (45, 130, 64, 1, "raw"), (9, 50, 32, 1, "unit"), (45, 130, 64, 2, "raw"), (61, 97, 128, 2, "unit"),
+    (45, 130, 64, 4, "raw"), (33, 49, 32, 4, "unit"), (70, 130, 64, 5, "raw"), (23, 41, 128, 5, "unit"),
+    (70, 130, 64, 6, "raw"), (25, 49, 36, 6, "unit"), (70, 130, 64, 8, "raw"), (35, 33, 192, 8, "unit"),
+    (300, 90, 32, 5, "raw"), (300, 70, 32, 8, "raw"), (40, 60, 32, 9, "raw"),
+    (70, 130, 64, 9, "raw"), (41, 77, 128, 9, "unit"), (70, 130, 64, 10, "raw"), (300, 50, 32, 10, "unit"),
+    (30, 60, 32, 11, "raw"),
 ])
 def test_ssd_vs_oracle(sm, H, W, D, k, scale):
     left, right, _ = synth.random_dot_pair(H, W, D, seed=H + W, scale=scale)
@@ -656,7 +664,10 @@ def test_birchfield_with_winner_takes_all_folded_in(sm, H, W, D, scale):
 
 @pytest.mark.parametrize("H,W,D,k,scale", [(21, 45, 64, 7, "unit"), (33, 150, 128, 7, "raw"), (40, 70, 192, 7, "raw"),
                                             (17, 203, 256, 3, "unit"), (30, 9, 64, 7, "raw"), (12, 50, 36, 7, "raw"),
-                                            (64, 96, 4, 3, "raw"), (375, 450, 64, 7, "raw"), (1080, 1920, 128, 7, "raw")])
+                                            (64, 96, 4, 3, "raw"), (375, 450, 64, 7, "raw"), (1080, 1920, 128, 7, "raw"),
+                                            (40, 90, 64, 1, "raw"), (40, 90, 64, 2, "unit"), (40, 90, 64, 4, "raw"),
+                                            (40, 90, 64, 5, "unit"), (40, 90, 64, 6, "raw"), (40, 90, 64, 8, "raw"),
+                                            (40, 90, 64, 9, "raw"), (40, 90, 64, 10, "unit")])
 def test_ssd_with_winner_takes_all_folded_in(sm, H, W, D, k, scale):
     """stm_ssd_wta_f32: the map is EXACTLY WinnerTakesAll of the SSD volume (same kernel arithmetic,
     first-minimum rule across the disparity chunks of different CTAs, +inf for d > x), without the
@@ -693,8 +704,8 @@ def test_ssd_with_winner_takes_all_unsupported_shapes_fall_back(sm):
     l, r = cuda(left), cuda(right)
     wta = sm.disparity_reduce.WinnerTakesAll()
     assert sm.cost.SSD(30).cost_and_reduce(l, r) is None          # D % 4 != 0
-    assert sm.cost.SSD(32, 5).cost_and_reduce(l, r) is None       # window the packed kernel is not built for
-    for cost in (sm.cost.SSD(30), sm.cost.SSD(32, 5)):
+    assert sm.cost.SSD(32, 11).cost_and_reduce(l, r) is None       # window the packed kernel is not built for
+    for cost in (sm.cost.SSD(30), sm.cost.SSD(32, 11)):
         pipe = sm.Pipeline(cost, wta)
         assert torch.equal(pipe.estimate(l, r), wta(cost(l, r)))
 
