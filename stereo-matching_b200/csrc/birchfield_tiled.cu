@@ -315,7 +315,9 @@ int launch_birchfield_tiled(const float *left, const float *right, float *cost, 
     case 2: return run_birchfield_tiled<2>(left, right, cost, H, W, D, stream);
     case 3: return run_birchfield_tiled<3>(left, right, cost, H, W, D, stream);
     case 4: return run_birchfield_tiled<4>(left, right, cost, H, W, D, stream);
+    case 5: return run_birchfield_tiled<5>(left, right, cost, H, W, D, stream);
     case 6: return run_birchfield_tiled<6>(left, right, cost, H, W, D, stream);
+    case 7: return run_birchfield_tiled<7>(left, right, cost, H, W, D, stream);
     case 8: return run_birchfield_tiled<8>(left, right, cost, H, W, D, stream);
     default: return 1;
   }

@@ -93,7 +93,8 @@ def test_birchfield_golden_shift_relation(sm, golden, case):
     (21, 45, 16, "raw"), (21, 45, 32, "unit"), (12, 150, 128, "unit"), (30, 9, 64, "raw"),
     (8, 70, 192, "unit"),
     (5, 7, 4, "unit"),        # W < 8: straightforward kernel
-    (6, 61, 160, "unit"),     # 5 lane groups: straightforward kernel
+    (6, 61, 160, "unit"), (5, 90, 150, "raw"), (7, 77, 224, "unit"),   # 5 and 7 lane groups
+    (4, 50, 300, "unit"),     # 10 lane groups: straightforward kernel
     (4, 203, 256, "unit"),    # 8 lane groups, width not a multiple of 8
     (9, 33, 20, "unit"), (3, 1000, 96, "raw"),
     (4, 1920, 128, "unit"),   # 1080p scanlines: 46 KB of shared memory per CTA
