@@ -31,7 +31,7 @@ class Semiglobal:
         component as two fused sweeps (csrc/sgm_vsweep.cu): four passes over the volumes instead
         of eight.  The sum is associated per sweep (0, 1, 2+4+6, 3+5+7) -- within 1e-4 of the
         reference order (measured 1.3e-5 at 1080p), not bit-identical.  fused_sweeps=None
-        (default) uses them for volumes above 48 MB whose rows hold at least 704*128 values
+        (default) uses them for volumes above 48 MB whose rows hold at least 600*128 values
         (where they are faster), True always, False never (reference order).
         Shapes the sweeps do not handle (more than 13 columns per SM -- 26 at D <= 64 --, D not
         in {<= 32, 64, 65..96, 128, 129..160, 192, 256}) take the per-direction passes.
@@ -53,12 +53,14 @@ class Semiglobal:
 
     def _use_fused_sweeps(self, cost_volume: torch.Tensor) -> bool:
         if self.fused_sweeps is None:
-            # auto.  A sweep costs ~0.7 us per image row almost whatever the row holds (hand-off
-            # latency), a direction pass costs its bytes: break-even at 1080 rows is W*D ~ 90k
-            # (measured ~110k when the sweeps took 0.93 us per row; scaled); below 48 MB the
-            # concurrent directions win anyway.
+            # auto.  The two sweeps cost ~0.7-0.8 us per image row each almost whatever the row holds
+            # (hand-off latency); the directions (concurrent up to 384 MB, else one after the other)
+            # cost ~21 ps per pixel-disparity: break-even at W*D ~ 76k.  Measured (tools/
+            # sgm_schedule_ab.py, sweeps vs directions, ms): W*D/128 = 640: 0.93 vs 1.21 (720x1280x64),
+            # 0.73 vs 0.79 (480x640x128); 480: 1.73 vs 1.60 (1080x1920x32); 450: 0.72 vs 0.47
+            # (375x450x128).  Below 48 MB the concurrent directions win anyway.
             H, W, D = cost_volume.shape
-            return cost_volume.numel() * cost_volume.element_size() > (48 << 20) and W * D >= 704 * 128
+            return cost_volume.numel() * cost_volume.element_size() > (48 << 20) and W * D >= 600 * 128
         return bool(self.fused_sweeps)
 
     def __call__(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
