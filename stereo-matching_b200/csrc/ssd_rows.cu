@@ -36,7 +36,11 @@
 // streaming stores (0.43), 11 H warps (0.46, spills), V warps helping with H items (0.61, spills),
 // 8 / 9 H warps (0.328 / 0.362), staging dealt out statically per V warp (6 registers of state
 // instead of 18, no spills, but 0.310: eleven unrolled variants of the staging code).
+#include <algorithm>
 #include <cstdlib>
+#include <functional>
+#include <mutex>
+#include <vector>
 
 #include "stm_common.cuh"
 
@@ -398,6 +402,21 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
               o += rowstride;
             }
           }
+        } else if (!WTA && dfirst + 3 < D && ybase >= ya && ybase + WIN <= yb) {
+          // Left image border (some d > x): the same branch-free loop, the entries beyond x replaced by
+          // +inf with selects and still ONE 16-byte store.  Four scalar stores with a test each made the
+          // CTAs of the first column tiles several times slower than the others -- the critical path of
+          // a launch with few waves (1080p D=64 with long row chunks).
+          float *o = ocol + (size_t)ybase * rowstride;
+#pragma unroll
+          for (int i = 0; i < WIN; ++i) {
+            float out[4];
+            row_sum(i, out);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) out[j] = dfirst + j > x ? CUDART_INF_F : out[j];
+            __stcs(reinterpret_cast<float4 *>(o), make_float4(out[0], out[1], out[2], out[3]));
+            o += rowstride;
+          }
         } else {
 #pragma unroll
           for (int i = 0; i < WIN; ++i) {
@@ -458,6 +477,53 @@ ssd_rows_kernel(const float *__restrict__ left, const float *__restrict__ right,
   }
 }
 
+// Groups of WIN rows per row chunk (a chunk of m groups writes m*WIN - (WIN-1) output rows).  A CTA costs
+// one period per group plus ~1.5 for fill and drain, and the CTAs of one launch -- per_z of them per
+// chunk, the last chunk shorter -- are handed to the SMs in launch order: the makespan of that greedy
+// schedule is evaluated for every m and the best one kept (ties: the larger m).  The fixed m = 20 left
+// the last wave half empty where few CTAs exist per chunk (1080p D=32: 230 CTAs on 148 SMs, two waves
+// for 1.2 waves of work).
+static int ssd_pick_groups(int H, int per_z, int win, int sms) {
+  struct Entry { int H, per_z, win, sms, m; };
+  static std::mutex mu;
+  static Entry cache[8];
+  static int used = 0, next = 0;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    for (int i = 0; i < used; ++i)
+      if (cache[i].H == H && cache[i].per_z == per_z && cache[i].win == win && cache[i].sms == sms) return cache[i].m;
+  }
+  auto cost = [&](int rows) { return (double)((rows + win - 1 + win - 1) / win) + 1.5; };  // groups + 1 periods + fill
+  double best = 1e300;
+  int best_m = 2;
+  std::vector<double> sm((size_t)sms);
+  for (int m = 2; m <= 48; ++m) {
+    const int rows = m * win - (win - 1);
+    const int ny = (H + rows - 1) / rows;
+    const int last = H - (ny - 1) * rows;
+    // full chunks: uniform jobs in launch order -> SM i gets q or q + 1 of them
+    const long long F = (long long)per_z * (ny - 1);
+    const double cf = cost(rows), cp = cost(last);
+    const long long q = F / sms, r = F % sms;
+    for (int i = 0; i < sms; ++i) sm[(size_t)i] = cf * (double)(q + (i < r ? 1 : 0));
+    // the last chunk's CTAs go to whichever SM is free first
+    std::make_heap(sm.begin(), sm.end(), std::greater<double>());
+    for (int j = 0; j < per_z; ++j) {
+      std::pop_heap(sm.begin(), sm.end(), std::greater<double>());
+      sm.back() += cp;
+      std::push_heap(sm.begin(), sm.end(), std::greater<double>());
+    }
+    const double span = *std::max_element(sm.begin(), sm.end());
+    if (span <= best * (1.0 + 1e-9)) { best = span; best_m = m; }
+    if (ny == 1) break;  // larger chunks change nothing
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  cache[next] = Entry{H, per_z, win, sms, best_m};
+  next = (next + 1) % 8;
+  if (used < 8) ++used;
+  return best_m;
+}
+
 template <int K, int RUNS, int NH, bool WTA>
 static int run_ssd_rows(const float *left, const float *right, float *cost, unsigned long long *keys, int H, int W,
                         int D, cudaStream_t stream) {
@@ -476,14 +542,16 @@ static int run_ssd_rows(const float *left, const float *right, float *cost, unsi
   const int nx = (W + C::TX - 1) / C::TX;
   const int nd = (D + C::DC - 1) / C::DC;
   // Row chunks of m*WIN - (WIN-1) output rows: such a chunk reads exactly m groups of WIN input
-  // rows.  ~128 rows per chunk as in ssd_tiled.cu (many short CTAs balance over the SMs and
-  // spread the store stream); small images: at least one CTA per SM while a chunk keeps >= 2 groups.
-  int m = 20;  // 1080p D=128: 0.423 ms with 5 groups per chunk, 0.360 with 10, 0.350 with 20 (measured)
+  // rows (1080p D=128, K=7: 0.423 ms with 5 groups per chunk, 0.360 with 10, 0.350 with 20, measured).
+  int m = ssd_pick_groups(H, nx * nd, C::WIN, num_sms());
   {
-    static const char *force = getenv("STM_DEBUG_SSD_GROUPS");  // developer knob: groups per chunk
+    static const char *force = getenv("STM_DEBUG_SSD_GROUPS");  // developer knob: groups per chunk; 0: the old fixed 20
     if (force && atoi(force) > 0) m = atoi(force);
+    else if (force && force[0] == '0') {
+      m = 20;
+      while (m > 2 && (long long)nx * nd * ((H + (m * C::WIN - C::WIN + 1) - 1) / (m * C::WIN - C::WIN + 1)) < num_sms()) --m;
+    }
   }
-  while (m > 2 && (long long)nx * nd * ((H + (m * C::WIN - C::WIN + 1) - 1) / (m * C::WIN - C::WIN + 1)) < num_sms()) --m;
   const int rows = m * C::WIN - (C::WIN - 1);
   const int ny = (H + rows - 1) / rows;
   if (nd > 65535 || ny > 65535) return fail(STM_EUNSUPPORTED, "ssd: shape too large");
