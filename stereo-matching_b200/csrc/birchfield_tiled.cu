@@ -19,6 +19,7 @@
 // Taps outside [d, W) contribute an exact +0 in the same left-to-right order, so the result
 // is bit-identical to the straightforward kernel (and to the oracle's restatement).
 // HBM traffic = the 4 B/pix-disp store of C; the scanlines come from L2.
+#include <cmath>
 #include <cstdlib>
 #include <type_traits>
 
@@ -150,14 +151,17 @@ __device__ __forceinline__ u64 add2(u64 a, u64 b) {
 template <int NJ, bool WTA>
 __global__ void __launch_bounds__(256)
 birchfield_row_packed_kernel(const float *__restrict__ left, const float *__restrict__ right,
-                             float *__restrict__ cost, int32_t *__restrict__ disp, int H, int W) {
+                             float *__restrict__ cost, int32_t *__restrict__ disp, int H, int W, int part_w) {
   using namespace bt2;
   static_assert(NJ % 2 == 0, "disparity groups are processed in pairs");
   constexpr int D = 32 * NJ, NP = NJ / 2;
   extern __shared__ float4 smq[];
   float4 *sLq = smq;               // [W + 8]:      pixel p at index p + 4,      p in [-4, W + 3]
   float4 *sRq = smq + (W + 8);     // [W + D + 8]:  pixel q at index q + D + 4,  q in [-D - 4, W + 3]
-  const int y = blockIdx.x;
+  // A CTA owns the columns [X0, X1) of scanline y (part_w = W: the whole line).  Several parts per
+  // line make the work units shorter: 1080 lines on 148 SMs are 7.3 lines per SM, i.e. 8 on the
+  // busiest one (measured: 1184 lines take the time of 1080).
+  const int y = blockIdx.x, X0 = blockIdx.y * part_w, X1 = min(W, X0 + part_w);
   const float *lrow = left + (size_t)y * W, *rrow = right + (size_t)y * W;
   const float4 sentinel = make_float4(0.f, 0.f, -CUDART_INF_F, -CUDART_INF_F);
 
@@ -168,15 +172,17 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
     const float a = 0.5f * (v + m), b = 0.5f * (v + n);
     return make_float4(v, v, -fmaxf(a, fmaxf(b, v)), fminf(a, fminf(b, v)));
   };
-  for (int i = threadIdx.x; i < W + 8; i += blockDim.x) sLq[i] = record(lrow, i - 4);
-  for (int i = threadIdx.x; i < W + D + 8; i += blockDim.x) sRq[i] = record(rrow, i - D - 4);
+  // only what the part reads: left pixels X0-4 .. X1+3, right pixels X0-D-4 .. X1+3 (same indices as
+  // for a whole line)
+  for (int i = X0 + threadIdx.x; i < X1 + 8; i += blockDim.x) sLq[i] = record(lrow, i - 4);
+  for (int i = X0 + threadIdx.x; i < X1 + D + 8; i += blockDim.x) sRq[i] = record(rrow, i - D - 4);
   __syncthreads();
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  const int chunk = (((W + nw - 1) / nw) + 7) & ~7;  // multiple of 8: window slots stay static
-  const int xa = warp * chunk;
-  const int xb = min(W, xa + chunk);
-  if (xa >= W) return;
+  const int chunk = (((X1 - X0 + nw - 1) / nw) + 7) & ~7;  // multiple of 8 (and so is X0): window slots stay static
+  const int xa = X0 + warp * chunk;
+  const int xb = min(X1, xa + chunk);
+  if (xa >= X1) return;
   const u64 one_neg = pk(1.f, -1.f);
   const float4 *rbase = sRq + (D + 4 - lane);  // + p - 32 j
 
@@ -260,6 +266,20 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
   if (x0 < xb) block8(std::true_type{}, std::true_type{}, x0);
 }
 
+// Parts per scanline.  The SMs take lines as they become free, so a launch ends when the busiest SM
+// has done ceil(H / SMs) of them: the idle share is 1 - (H / SMs) / ceil(H / SMs) -- 9 % at 1080
+// lines on 148 SMs, 3 % at 720 or 2160.  Two half lines per line halve the unit at the price of
+// D + 8 more staged pixels per part.  Measured at 1920 columns (tools/stage_bench.py with
+// STM_DEBUG_BT_PARTS = 1 / 2 / 3 / 4): 1080 lines D=128 0.228 / 0.223 / 0.223 / 0.229 ms, D=192
+// 0.296 / 0.280 / 0.280 / 0.290; 720 lines 0.105 / 0.108; 2160 x 3840 0.671 / 0.716.  So: two parts
+// where whole lines idle more than 6 % of the machine and half lines do better, else one.
+static int bt_parts(int H, int W) {
+  if (W < 256) return 1;
+  const double sms = (double)num_sms();
+  auto idle = [&](int units) { const double per = units / sms; return 1.0 - per / ceil(per); };
+  return (idle(H) > 0.06 && idle(2 * H) < idle(H) - 0.03) ? 2 : 1;
+}
+
 template <int NJ, bool WTA>
 static int run_birchfield_packed(const float *left, const float *right, float *cost, int32_t *disp, int H,
                                  int W, cudaStream_t stream) {
@@ -267,7 +287,16 @@ static int run_birchfield_packed(const float *left, const float *right, float *c
   auto kernel = birchfield_row_packed_kernel<NJ, WTA>;
   if (smem > 48 * 1024)  // per device and cheap: set on every call (stm_common.cuh, per-device state)
     STM_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kernel<<<H, 256, smem, stream>>>(left, right, cost, disp, H, W);
+  int parts = bt_parts(H, W);
+  {
+    static const char *force = getenv("STM_DEBUG_BT_PARTS");  // developer knob
+    if (force && atoi(force) > 0) parts = atoi(force);
+  }
+  int part_w = (((W + parts - 1) / parts) + 63) & ~63;   // 8 warps x 8 columns
+  if (part_w > W) part_w = (W + 7) & ~7;
+  const int ny = (W + part_w - 1) / part_w;
+  if (ny > 65535) return 1;
+  kernel<<<dim3(H, ny), 256, smem, stream>>>(left, right, cost, disp, H, W, part_w);
   return check_launch("birchfield_row_packed_kernel");
 }
 
