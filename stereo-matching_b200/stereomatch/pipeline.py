@@ -51,9 +51,11 @@ class Pipeline:
 
     def _fold_pays(self, left_image: torch.Tensor) -> bool:
         """Birchfield + WTA in one kernel wins at every size.  SSD + WTA pays for its atomics and
-        shuffles: a win when the volume would go through HBM (1080p D=128: 0.45 -> 0.42 ms, and no
-        1 GB volume), a loss while the volume stays in L2 (450x375 D=64: 0.057 -> 0.070 ms), so the
-        fold is used above 48 MB -- the threshold of the other size rules (aggregation.py).
+        shuffles: when the volume would go through HBM it takes the time of the two stages
+        (1080p D=128: 0.43 ms against 0.42-0.45, measured before and after the SSD kernel got
+        faster) and needs no 1 GB volume; while the volume stays in L2 it loses (450x375 D=64:
+        0.053 -> 0.064 ms).  So the fold is used above 48 MB -- the threshold of the other size
+        rules (aggregation.py) -- for its memory, not its speed.
         fuse_cost_and_reduce = "always" forces it."""
         if type(self.cost) is not SSD or self.fuse_cost_and_reduce == "always":
             return True
