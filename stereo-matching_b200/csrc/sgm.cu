@@ -690,11 +690,19 @@ size_t sgm_workspace_bytes_flags(int H, int W, int D, unsigned flags) {
 // direction 4 on portrait ones (sgm_by_direction_portrait; the defective descriptors precede the
 // corner diagonal's own in the reference's list).  Pixels a defective direction never visits hold 0
 // in its buffer (memset by the caller).
-template <int VEC>
+// GROUP > 0 (VEC = 4, D = 4 * GROUP in {32, 64, 128}): the GROUP consecutive threads that hold a pixel's
+// sums also take its winner -- first minimum, NaN never wins, NaN at d = 0 -> 0, all +inf -> 0: the rule
+// of wta.cu / reference src/winners_take_all.cu:21-40 -- by a butterfly under the full mask (xor
+// distances below GROUP stay inside the pixel's lanes), so the separate WTA pass over the volume is
+// not needed; with store_out = 0 (STM_SGM_DISPARITY_ONLY) the sums are not written either.
+template <int VEC, int GROUP>
 __global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict__ bufs,
-                                size_t n_vec, size_t stride, int H, int W, int D, int accumulate) {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_vec) return;
+                                size_t n_vec, size_t stride, int H, int W, int D, int accumulate,
+                                int32_t *__restrict__ disp, int store_out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (GROUP == 0 && i >= n_vec) return;
+  const bool live = i < n_vec;      // GROUP > 0: n_vec is a multiple of GROUP, so a pixel's threads agree
+  if (!live) i = n_vec - 1;
   const size_t e = i * VEC;           // first element of this thread
   const size_t pixel = e / D;
   const int x = (int)(pixel % W), y = (int)(pixel / W);
@@ -735,10 +743,29 @@ __global__ void sgm_sum8_kernel(float *__restrict__ out, const float *__restrict
     if (dir == 5 && !portrait) add_b(extra5);
     if (dir == 7) add_b(extra7);
   }
-  if constexpr (VEC == 4) {
-    *reinterpret_cast<float4 *>(out + e) = make_float4(s[0], s[1], s[2], s[3]);
-  } else {
-    out[e] = s[0];
+  if (live && (GROUP == 0 || store_out)) {
+    if constexpr (VEC == 4) {
+      *reinterpret_cast<float4 *>(out + e) = make_float4(s[0], s[1], s[2], s[3]);
+    } else {
+      out[e] = s[0];
+    }
+  }
+  if constexpr (GROUP > 0) {
+    const int d0 = (int)(e - pixel * D);   // this thread's first disparity
+    float best = CUDART_INF_F;
+    int bd = 0x7fffffff;
+#pragma unroll
+    for (int k = 0; k < VEC; ++k)
+      if (s[k] < best) { best = s[k]; bd = d0 + k; }   // strict: the lowest d keeps a tie; NaN never passes
+    int nan0 = (d0 == 0 && s[0] != s[0]) ? 1 : 0;
+#pragma unroll
+    for (int w = 1; w < GROUP; w <<= 1) {
+      const float ob = __shfl_xor_sync(FULL, best, w);
+      const int od = __shfl_xor_sync(FULL, bd, w);
+      nan0 |= __shfl_xor_sync(FULL, nan0, w);
+      if (ob < best || (ob == best && od < bd)) { best = ob; bd = od; }
+    }
+    if (live && d0 == 0) disp[pixel] = (nan0 || bd == 0x7fffffff) ? 0 : bd;
   }
 }
 
@@ -938,17 +965,26 @@ static int sgm_concurrent(const float *cost, const float *image, float *out, int
     }
   }
   const int accumulate = (flags & STM_SGM_OVERWRITE) ? 0 : 1;
-  if (D % 4 == 0) {
-    const size_t n_vec = N / 4;
-    sgm_sum8_kernel<4><<<(unsigned)((n_vec + 255) / 256), 256, 0, stream>>>(out, bufs, n_vec, N, H, W,
-                                                                          D, accumulate);
+  const size_t n_vec = N / 4;
+  const unsigned blocks4 = (unsigned)((n_vec + 255) / 256);
+  const int store_out = (flags & STM_SGM_DISPARITY_ONLY) ? 0 : 1;
+  bool emitted = false;
+  if (disp && (D == 32 || D == 64 || D == 128)) {
+    // the sum kernel takes the winner itself: no pass over the volume for the argmin, no store of the
+    // sums when only the map is wanted (375x450x128: 0.47 -> ~0.43 ms)
+    if (D == 128) sgm_sum8_kernel<4, 32><<<blocks4, 256, 0, stream>>>(out, bufs, n_vec, N, H, W, D, accumulate, disp, store_out);
+    else if (D == 64) sgm_sum8_kernel<4, 16><<<blocks4, 256, 0, stream>>>(out, bufs, n_vec, N, H, W, D, accumulate, disp, store_out);
+    else sgm_sum8_kernel<4, 8><<<blocks4, 256, 0, stream>>>(out, bufs, n_vec, N, H, W, D, accumulate, disp, store_out);
+    emitted = true;
+  } else if (D % 4 == 0) {
+    sgm_sum8_kernel<4, 0><<<blocks4, 256, 0, stream>>>(out, bufs, n_vec, N, H, W, D, accumulate, nullptr, 1);
   } else {
-    sgm_sum8_kernel<1><<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(out, bufs, N, N, H, W, D,
-                                                                      accumulate);
+    sgm_sum8_kernel<1, 0><<<(unsigned)((N + 255) / 256), 256, 0, stream>>>(out, bufs, N, N, H, W, D, accumulate,
+                                                                           nullptr, 1);
   }
   rc = check_launch("sgm_sum8_kernel");
   if (rc) return rc;
-  if (disp) return launch_wta(out, disp, H, W, D, stream);
+  if (disp && !emitted) return launch_wta(out, disp, H, W, D, stream);
   return STM_OK;
 }
 
