@@ -931,6 +931,130 @@ static int sgm_fused_overlap(const float *cost, const float *image, float *out, 
   return STM_OK;
 }
 
+// ---- D = 64, concurrent schedule: TWO paths per warp --------------------------------------------
+// With 64 disparities a warp of sgm_path_kernel holds two per lane: every instruction of the step does
+// half the work it does at D = 128, and eight directions at once are bound by instruction issue
+// (450x375x64: ~0.2 ms for the directions where their bytes need a third).  Here a warp runs two
+// adjacent paths of the direction, one per 16 lanes, four disparities per lane: the step is the same
+// arithmetic in the same order (bit-identical), d-1 / d+1 come from shuffles that stay inside the half
+// (full mask, per-lane source), and the minimum over a path's 64 values is a four-step butterfly in the
+// half instead of one redux over the warp.  Only what the concurrent schedule needs: L written to the
+// direction's buffer, no accumulation, no corner replays (the sum kernel does both).
+struct HalfCtx {
+  int src_lo, src_hi;
+  bool first, last, excl_last;
+};
+__device__ __forceinline__ float half_min(const float (&v)[4], const HalfCtx &cx) {
+  float m = cx.excl_last ? CUDART_INF_F : v[3];
+  m = fminf(m, fminf(v[0], fminf(v[1], v[2])));
+#pragma unroll
+  for (int w = 1; w < 16; w <<= 1) m = fminf(m, __shfl_xor_sync(FULL, m, w));
+  return m;
+}
+// lv_sgm_step<1, 4> for one half: L[d] = (c[d] + min(L[d], L[d-1]+P1, L[d+1]+P1, m+P2')) - m
+__device__ __forceinline__ void half_sgm_step(float (&L)[4], const float (&c)[4], float p1, float p2_adj,
+                                              const HalfCtx &cx) {
+  const float m = half_min(L, cx);
+  const float from_left = __shfl_sync(FULL, L[3], cx.src_lo);
+  const float from_right = __shfl_sync(FULL, L[0], cx.src_hi);
+  const float far = __fadd_rn(m, p2_adj);
+  float lo[4], hi[4];
+  lo[0] = cx.first ? CUDART_INF_F : from_left;
+  lo[1] = L[0]; lo[2] = L[1]; lo[3] = L[2];
+  hi[0] = L[1]; hi[1] = L[2]; hi[2] = L[3];
+  hi[3] = cx.last ? CUDART_INF_F : from_right;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float a = __fadd_rn(lo[j], p1);
+    const float b = __fadd_rn(hi[j], p1);
+    const float best = fminf(fminf(L[j], a), fminf(b, far));
+    L[j] = __fsub_rn(__fadd_rn(c[j], best), m);
+  }
+}
+
+__global__ void __launch_bounds__(128)
+sgm_path_half64_kernel(const float *__restrict__ cost, const float *__restrict__ image, float *__restrict__ out,
+                       int H, int W, float p1, float p2, int dir, int path_count, int min_limit) {
+  constexpr int D = 64, PF = 8;
+  const int lane = threadIdx.x & 31, l16 = lane & 15, half = lane >> 4;
+  const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (2 * w >= path_count) return;  // warp-uniform
+  int path = 2 * w + half;
+  const bool have = path < path_count;   // an odd count leaves the last warp's second half idle:
+  if (!have) path = path_count - 1;      // it shadows the first half and stores nothing
+  const PathGeom g = sgm_path_geom(dir, path, H, W);
+  const bool writes = have && g.mult != 0;   // paths the reference never runs: the buffer holds 0 (memset)
+  HalfCtx cx;
+  cx.src_lo = (lane & 16) | ((l16 + 15) & 15);
+  cx.src_hi = (lane & 16) | ((l16 + 1) & 15);
+  cx.first = l16 == 0;
+  cx.last = l16 == 15;
+  cx.excl_last = l16 * 4 + 3 >= min_limit;
+  const long long pix0 = (long long)g.sy * W + g.sx;
+  const long long step = (long long)g.dy * W + g.dx;
+  const long long step_d = step * D;
+  const int n = g.n;
+  const int n_max = max(n, __shfl_xor_sync(FULL, n, 16));
+  const float *cfetch = cost + pix0 * D + l16 * 4;
+  const float *ifetch = image + pix0;
+  float *optr = out + pix0 * D + l16 * 4;
+  auto load4 = [](float (&r)[4], const float *q) {
+    const float4 t = ld_stream4(q);
+    r[0] = t.x; r[1] = t.y; r[2] = t.z; r[3] = t.w;
+  };
+  float L[4];
+  load4(L, cfetch);
+  if (writes) st_stream4(optr, make_float4(L[0], L[1], L[2], L[3]));
+  if (n_max == 1) return;
+  // The adaptive penalty max(P1, P2/|dI|) (an IEEE division, ~15 dependent instructions) depends on the
+  // intensities only.  Lane u of a half computes it ONCE for pixel i + u of the current group of PF
+  // steps; a shuffle per step hands it out.  Evaluated by every lane at every step it is part of the
+  // in-order instruction stream of a latency-bound chain (sgm_row.cu did the same for the same reason).
+  const float *ibase = image + pix0;
+  auto intensity_of = [&](int i) { return __ldg(ibase + (long long)min(i, n - 1) * step); };  // lane u: pixel i + u
+  const int hbase = lane & 16;
+  float iprev_grp = intensity_of(0);              // every lane: pixel 0 (the carry into group 1 .. PF)
+  float icur = intensity_of(1 + (l16 & (PF - 1)));
+  float cbuf[PF][4];
+  int left = n - 1;
+#pragma unroll
+  for (int u = 0; u < PF; ++u) {
+    if (left > 0) { cfetch += step_d; --left; }
+    load4(cbuf[u], cfetch);
+  }
+  bool first_group = true;
+  for (int i = 1; i < n_max; i += PF) {
+    const float inext = intensity_of(i + PF + (l16 & (PF - 1)));
+    const float left_px = __shfl_sync(FULL, icur, hbase | ((l16 + 15) & 15));
+    const float carry = first_group ? iprev_grp : __shfl_sync(FULL, iprev_grp, hbase | (PF - 1));
+    const float p2_grp = sgm_p2_adjusted(p1, p2, icur, (l16 & (PF - 1)) == 0 ? carry : left_px);
+    first_group = false;
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+      float c[4] = {cbuf[u][0], cbuf[u][1], cbuf[u][2], cbuf[u][3]};
+      if (left > 0) { cfetch += step_d; --left; }
+      load4(cbuf[u], cfetch);
+      half_sgm_step(L, c, p1, __shfl_sync(FULL, p2_grp, hbase | u), cx);
+      optr += step_d;
+      if (writes && i + u < n) st_stream4(optr, make_float4(L[0], L[1], L[2], L[3]));
+    }
+    iprev_grp = icur;
+    icur = inext;
+  }
+}
+
+static bool sgm_half64_enabled() {
+  static const char *off = getenv("STM_DEBUG_SGM_HALF");  // developer knob: "0" disables
+  return !(off && off[0] == '0');
+}
+static int launch_sgm_half64(const float *cost, const float *image, float *out, int H, int W, float p1, float p2,
+                             int dir, int min_limit, cudaStream_t stream) {
+  const int np = sgm_num_paths(dir, H, W);
+  const int warps = (np + 1) / 2;
+  sgm_path_half64_kernel<<<(warps + 3) / 4, 128, 0, stream>>>(cost, image, out, H, W, p1, p2, dir, np, min_limit);
+  return check_launch("sgm_path_half64_kernel");
+}
+
 int launch_wta(const float *, int32_t *, int, int, int, cudaStream_t);  // wta.cu
 
 template <int NV, int VW>
@@ -955,8 +1079,11 @@ static int sgm_concurrent(const float *cost, const float *image, float *out, int
     if (((dir == 5 && W != H) || (dir == 7 && W > H)) &&
         cudaMemsetAsync(b, 0, N * sizeof(float), s) != cudaSuccess)
       return fail(STM_ECUDA, "sgm: cudaMemsetAsync failed");
-    rc = run_direction<NV, VW>(cost, image, b, H, W, D, p1, p2, dir, 0, sgm_num_paths(dir, H, W),
-                               min_limit, 0u, nullptr, -1, s);
+    if (D == 64 && sgm_half64_enabled() && !((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(b)) & 15))
+      rc = launch_sgm_half64(cost, image, b, H, W, p1, p2, dir, min_limit, s);   // two paths per warp
+    else
+      rc = run_direction<NV, VW>(cost, image, b, H, W, D, p1, p2, dir, 0, sgm_num_paths(dir, H, W),
+                                 min_limit, 0u, nullptr, -1, s);
     if (rc) return rc;
     if (dir > 0) {
       if (cudaEventRecord(aux->join[dir - 1], s) != cudaSuccess ||
