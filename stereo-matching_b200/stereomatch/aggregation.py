@@ -31,8 +31,9 @@ class Semiglobal:
         component as two fused sweeps (csrc/sgm_vsweep.cu): four passes over the volumes instead
         of eight.  The sum is associated per sweep (0, 1, 2+4+6, 3+5+7) -- within 1e-4 of the
         reference order (measured 1.3e-5 at 1080p), not bit-identical.  fused_sweeps=None
-        (default) uses them for volumes above 48 MB whose rows hold at least 600*128 values
-        (where they are faster), True always, False never (reference order).
+        (default) uses them for volumes above 48 MB where a cost model of both schedules says
+        they are faster (about W*D >= 600*128, more for D > 128 and for few rows), True always,
+        False never (reference order).
         Shapes the sweeps do not handle (more than 13 columns per SM -- 26 at D <= 64 --, D not
         in {<= 32, 64, 65..96, 128, 129..160, 192, 256}) take the per-direction passes.
       * overlap (with the fused sweeps; default on): the two horizontal passes run on a helper
@@ -53,14 +54,20 @@ class Semiglobal:
 
     def _use_fused_sweeps(self, cost_volume: torch.Tensor) -> bool:
         if self.fused_sweeps is None:
-            # auto.  The two sweeps cost ~0.7-0.8 us per image row each almost whatever the row holds
-            # (hand-off latency); the directions (concurrent up to 384 MB, else one after the other)
-            # cost ~21 ps per pixel-disparity: break-even at W*D ~ 76k.  Measured (tools/
-            # sgm_schedule_ab.py, sweeps vs directions, ms): W*D/128 = 640: 0.93 vs 1.21 (720x1280x64),
-            # 0.73 vs 0.79 (480x640x128); 480: 1.73 vs 1.60 (1080x1920x32); 450: 0.72 vs 0.47
-            # (375x450x128).  Below 48 MB the concurrent directions win anyway.
+            # auto: a cost model fitted to tools/sgm_schedule_ab.py (ms, sweeps vs directions):
+            #   720x1280x64 0.93 / 1.20   480x640x128 0.73 / 0.79   400x700x128 0.65 / 0.67
+            #   400x600x128 0.62 / 0.59   500x560x192 1.10 / 1.08   375x450x192 1.04 / 0.68
+            #   300x500x256 0.89 / 0.74   1080x1920x32 1.73 / 1.60  375x450x128 0.72 / 0.47
+            # The two sweeps cost a row period per image row each -- ~0.68 us up to 128 disparities
+            # (hand-off latency), proportionally more above -- plus ~0.1 ms of fixed cost; the eight
+            # directions (concurrent up to 384 MB, else one after the other) cost ~19.5 ps per
+            # pixel-disparity.  Below 48 MB the concurrent directions win anyway.
             H, W, D = cost_volume.shape
-            return cost_volume.numel() * cost_volume.element_size() > (48 << 20) and W * D >= 600 * 128
+            if cost_volume.numel() * cost_volume.element_size() <= (48 << 20):
+                return False
+            sweeps_us = 2.0 * H * 0.68 * max(1.0, D / 128.0) + 100.0
+            directions_us = 19.5e-6 * H * W * D
+            return sweeps_us < directions_us
         return bool(self.fused_sweeps)
 
     def __call__(self, cost_volume: torch.Tensor, left_image: torch.Tensor,
