@@ -1,5 +1,6 @@
 """Random-shape parity of every stage against the oracle (developer tool; the fixed shapes live in tests/).
-    python tools/fuzz_parity.py [cases] [seed]
+    python tools/fuzz_parity.py [cases] [seed] [big]
+big: mid-size volumes (40 .. 400 MB: the concurrent / fused-sweep / sequential decision of the auto rule).
 Small shapes so that the C oracle answers at once; every schedule of the aggregation; prints one line per
 failure and a summary, exit code 1 on any failure."""
 import sys
@@ -18,6 +19,7 @@ cases = int(sys.argv[1]) if len(sys.argv) > 1 else 120
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 7)
 DS = [4, 8, 12, 16, 20, 32, 36, 48, 64, 64, 64, 80, 96, 100, 128, 128, 150, 160, 192, 224, 256]
 fails = []
+BIG = len(sys.argv) > 3 and sys.argv[3] == "big"
 
 
 def cuda(a):
@@ -44,7 +46,11 @@ for n in range(cases):
     if n % 7 == 0:
         W = int(rng.integers(140, 700))   # several column tiles / CTAs of the sweeps
     D = int(rng.choice(DS))
-    k = int(rng.integers(0, 12))
+    if BIG:
+        H, W, D = int(rng.integers(150, 520)), int(rng.integers(250, 800)), int(rng.choice([64, 96, 128, 160, 192]))
+        if n % 3 == 0:
+            H, W = W, H   # portrait
+    k = int(rng.integers(1, 4)) if BIG else int(rng.integers(0, 12))   # (the oracle's SSD is (2k)^2 taps per output)
     scale = "raw" if n % 2 == 0 else "unit"
     shape = (H, W, D, k, scale)
     left, right, _ = synth.random_dot_pair(H, W, D, seed=1000 + n, scale=scale)
@@ -71,6 +77,15 @@ for n in range(cases):
         fails.append(("dp", shape)); print("FAIL dp", shape, flush=True)
     # aggregation: default (concurrent), sequential, fused sweeps (overlapped and plain), and the folds
     osgm = O.sgm(ossd, left, 0.1, 0.2)
+    if BIG:   # what the auto rule picks, volume and map
+        auto = sm.aggregation.Semiglobal()
+        close(auto(c, l), osgm, False, "sgm_auto", shape)
+        v, d_ = auto.aggregate_and_reduce(c, l)
+        if not torch.equal(d_, wta(v)):
+            fails.append(("sgm_auto_wta", shape)); print("FAIL sgm_auto_wta", shape, flush=True)
+        _, d2 = auto.aggregate_and_reduce(c, l, keep_volume=False)
+        if float((d2 != d_).float().mean()) > 1e-3:
+            fails.append(("sgm_auto_wta_only", shape)); print("FAIL sgm_auto_wta_only", shape, flush=True)
     seq = sm.aggregation.Semiglobal(concurrent_directions=False, fused_sweeps=False)(c, l).clone()
     close(seq, osgm, False, "sgm_sequential", shape)
     conc_op = sm.aggregation.Semiglobal(fused_sweeps=False)
