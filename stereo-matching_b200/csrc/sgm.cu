@@ -1144,6 +1144,7 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   if (m.NV == NV_ && m.VW == VW_)   \
     rc = sgm_fused_overlap<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, workspace, workspace_bytes, stream, disp);
       STM_SGM_FO(1, 4) STM_SGM_FO(1, 2) STM_SGM_FO(3, 2) STM_SGM_FO(1, 1) STM_SGM_FO(3, 1) STM_SGM_FO(5, 1)
+      STM_SGM_FO(2, 1) STM_SGM_FO(4, 1)   // ranges that are not a multiple of 32: the sweeps mask a vector map
 #undef STM_SGM_FO
       if (rc != 1) return rc;
     }
@@ -1151,6 +1152,7 @@ int launch_sgm(const float *cost, const float *image, float *out, int H, int W, 
   if (m.NV == NV_ && m.VW == VW_)   \
     rc = sgm_fused<NV_, VW_>(cost, image, out, H, W, D, p1, p2, flags, workspace, workspace_bytes, stream, disp);
     STM_SGM_FS(1, 4) STM_SGM_FS(2, 4) STM_SGM_FS(1, 2) STM_SGM_FS(3, 2) STM_SGM_FS(1, 1) STM_SGM_FS(3, 1) STM_SGM_FS(5, 1)
+    STM_SGM_FS(2, 1) STM_SGM_FS(4, 1)
 #undef STM_SGM_FS
     if (rc != 1) return rc;
   }

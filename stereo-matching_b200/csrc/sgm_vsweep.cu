@@ -513,9 +513,14 @@ __device__ __forceinline__ void add_scaled(LaneVec<NV, VW> &o, const LaneVec<NV,
   }
 }
 
-template <int NV, int VW, bool UP, bool WTA, int NS>
+// MASKED: D < DPAD with whole lane vectors beyond D (D % VW == 0): those lanes never load or store and
+// hold +inf costs -- exactly the reference's out-of-range neighbour value -- so a range such as
+// D = 96 or 100 runs the 4-wide lane map of D = 128 instead of scalar lanes.  VW == 1 maps always
+// mask (any D <= DPAD).
+template <int NV, int VW, bool UP, bool WTA, int NS, bool MASKED>
 __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int base, int j, int lane) {
   constexpr int DPAD = NV * 32 * VW;
+  constexpr bool kMask = MASKED || VW == 1;
   using C = Cfg<DPAD, NS>;
   constexpr int PF = C::PF;
   const int H = P.H, W = P.W, D = P.D;
@@ -549,7 +554,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       const int off = k * 32 * VW;
-      if ((VW > 1 || off + lane < D) && !(kDebug && (P.dbg & 32))) {
+      if ((!kMask || off + lane * VW < D) && !(kDebug && (P.dbg & 32))) {
         cp_async<VW * 4>(dc + off, cs + off);
         if constexpr (NS >= 2) cp_async<VW * 4>(dc + DPAD + off, ss + off);
         if constexpr (NS >= 3) cp_async<VW * 4>(dc + 2 * DPAD + off, xs + off);
@@ -609,18 +614,24 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       for (int extra_i = 2; extra_i < NS; ++extra_i) {
         LaneVec<NV, VW> x2;
         lv_lds<NV, VW>(x2, pf + e * NS * DPAD + extra_i * DPAD, 0);
-        if constexpr (VW == 1) {
+        if constexpr (kMask) {
 #pragma unroll
           for (int k = 0; k < NV; ++k)
-            if (k * 32 + lane >= D) x2.v[k][0] = 0.f;
+            if (k * 32 * VW + lane * VW >= D) {
+#pragma unroll
+              for (int q = 0; q < VW; ++q) x2.v[k][q] = 0.f;
+            }
         }
         add_weighted<NV, VW>(o, x2, 1);
       }
     }
-    if constexpr (VW == 1) {
+    if constexpr (kMask) {
 #pragma unroll
       for (int k = 0; k < NV; ++k)
-        if (k * 32 + lane >= D) { c.v[k][0] = CUDART_INF_F; o.v[k][0] = 0.f; }
+        if (k * 32 * VW + lane * VW >= D) {
+#pragma unroll
+          for (int q = 0; q < VW; ++q) { c.v[k][q] = CUDART_INF_F; o.v[k][q] = 0.f; }
+        }
     }
     const int en = e + 1 == PF ? 0 : e + 1;
     __syncwarp();                  // lane 0's penalty copy of row t+1 is visible to the warp
@@ -704,7 +715,9 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
       add_scaled<NV, VW>(o, LC, (float)(w_now >> 16));
       add_scaled<NV, VW>(o, LA, (float)(w_now & 0xffffu));
     }
-    if (store_vol && !(kDebug && (P.dbg & 32))) lv_store<NV, VW, true>(o, orow + x * D, 0, D - lane_off);
+    static_assert(!MASKED || NV == 1, "masked vector maps have one vector per lane");
+    if (store_vol && (!MASKED || lane_off < D) && !(kDebug && (P.dbg & 32)))
+      lv_store<NV, VW, true>(o, orow + x * D, 0, D - lane_off);
     if (emit_wta) lv_argmin_store<NV, VW>(o, lane, D, drow + x);
 
     mark(t, 3);
@@ -725,7 +738,7 @@ __device__ void column_warp(unsigned char *smem, const Params &P, int ncols, int
 
 // MINB = 2: the same kernel compiled for two CTAs per SM (64 registers), for images wider than
 // kCols columns per SM; only for the lane maps with at most two disparities per lane (D <= 64).
-template <int NV, int VW, bool UP, bool WTA, int NS, int MINB = 1>
+template <int NV, int VW, bool UP, bool WTA, int NS, int MINB = 1, bool MASKED = false>
 __global__ void __launch_bounds__(kThreads, MINB) sgm_vsweep_kernel(const Params P) {
   extern __shared__ __align__(128) unsigned char smem[];
   using C = Cfg<NV * 32 * VW, NS>;
@@ -746,7 +759,7 @@ __global__ void __launch_bounds__(kThreads, MINB) sgm_vsweep_kernel(const Params
   __syncthreads();
   if (wid == kCols) importer_warp<NV, VW>(smem, P, ncols, lane);
   else if (wid == kCols + 1) exporter_warp<NV, VW>(smem, P, lane);
-  else if (wid < ncols) column_warp<NV, VW, UP, WTA, NS>(smem, P, ncols, base, wid, lane);
+  else if (wid < ncols) column_warp<NV, VW, UP, WTA, NS, MASKED>(smem, P, ncols, base, wid, lane);
 }
 
 static size_t align256(size_t n) { return (n + 255) & ~(size_t)255; }
@@ -786,37 +799,37 @@ static size_t flags_and_rings_bytes(size_t dpad) {
 
 // The six variants of one lane map: (up?, argmin?, volume streams).  nullptr = does not fit in
 // shared memory for this lane map (three streams at D = 256).
-template <int NV, int VW, bool UP, bool WTA, int NS>
+template <int NV, int VW, bool UP, bool WTA, int NS, bool MASKED>
 static const void *variant(size_t *smem_bytes, int minb = 1) {
   using C = Cfg<NV * 32 * VW, NS>;
   if constexpr (C::kFits) {
     *smem_bytes = (size_t)C::kBytes;
     if (minb == 2) {
       if constexpr (NV * VW <= 2 && 2 * C::kBytes + 2048 <= 227 * 1024)
-        return (const void *)sgm_vsweep_kernel<NV, VW, UP, WTA, NS, 2>;
+        return (const void *)sgm_vsweep_kernel<NV, VW, UP, WTA, NS, 2, MASKED>;
       else
         return nullptr;
     }
-    return (const void *)sgm_vsweep_kernel<NV, VW, UP, WTA, NS>;
+    return (const void *)sgm_vsweep_kernel<NV, VW, UP, WTA, NS, 1, MASKED>;
   } else {
     *smem_bytes = 0;
     return nullptr;
   }
 }
-template <int NV, int VW>
+template <int NV, int VW, bool M = false>
 static const void *sweep_kernel(bool up, bool wta, int ns, size_t *smem_bytes, int minb = 1) {
   size_t *b = smem_bytes;
-  if (!up) return ns == 1 ? variant<NV, VW, false, false, 1>(b, minb) : variant<NV, VW, false, false, 2>(b, minb);
-  if (ns == 4) return wta ? variant<NV, VW, true, true, 4>(b, minb) : nullptr;  // Pipeline path only
-  if (ns == 3) return wta ? variant<NV, VW, true, true, 3>(b, minb) : variant<NV, VW, true, false, 3>(b, minb);
-  return wta ? variant<NV, VW, true, true, 2>(b, minb) : variant<NV, VW, true, false, 2>(b, minb);
+  if (!up) return ns == 1 ? variant<NV, VW, false, false, 1, M>(b, minb) : variant<NV, VW, false, false, 2, M>(b, minb);
+  if (ns == 4) return wta ? variant<NV, VW, true, true, 4, M>(b, minb) : nullptr;  // Pipeline path only
+  if (ns == 3) return wta ? variant<NV, VW, true, true, 3, M>(b, minb) : variant<NV, VW, true, false, 3, M>(b, minb);
+  return wta ? variant<NV, VW, true, true, 2, M>(b, minb) : variant<NV, VW, true, false, 2, M>(b, minb);
 }
 
 // CTAs for an image W columns wide (all co-resident, 2..kCols slots each), or 0.  group 0: the plain
 // pair of sweeps (NS = 2); 1: the overwriting down sweep and the three-stream up sweep as well; 2: and
 // the four-stream one.  *minb = CTAs per SM the kernels must be compiled for: 1, or 2 when the image
 // is wider than kCols columns per SM and the lane map has a two-CTA build (D <= 64).
-template <int NV, int VW>
+template <int NV, int VW, bool M = false>
 static int ctas(int W, int group, int *minb_out) {
   static PerDeviceInt cache[3][2];  // per instantiation and device (attribute opt-in + occupancy)
   const int dev = device_slot();
@@ -829,7 +842,7 @@ static int ctas(int W, int group, int *minb_out) {
         if (group < 1 && ns != 2) continue;
         if (ns == 4 && group < 2) continue;
         size_t bytes = 0;
-        const void *k = sweep_kernel<NV, VW>(v != 0 && v != 3, v == 2 || v == 5 || v == 6, ns, &bytes, minb);
+        const void *k = sweep_kernel<NV, VW, M>(v != 0 && v != 3, v == 2 || v == 5 || v == 6, ns, &bytes, minb);
         int n = 0;
         if (k == nullptr) { per_sm = 0; break; }
         if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess ||
@@ -900,16 +913,16 @@ static int take_sweep_abort(unsigned *info3) {
   return 1;
 }
 
-template <int NV, int VW>
+template <int NV, int VW, bool M = false>
 static int run(const float *cost, const float *image, float *out, const float *extra, const float *extra2,
                int32_t *disp, int H, int W, int D, float p1, float p2, int min_limit, int up, bool store_vol,
                int ns, char *ws, cudaStream_t stream) {
   constexpr int DPAD = NV * 32 * VW;
   size_t smem_bytes = 0;
   int minb = 1;
-  const int G = ctas<NV, VW>(W, ns == 2 ? 0 : (ns == 4 ? 2 : 1), &minb);
+  const int G = ctas<NV, VW, M>(W, ns == 2 ? 0 : (ns == 4 ? 2 : 1), &minb);
   if (G < 1) return 1;
-  const void *kernel = sweep_kernel<NV, VW>(up != 0, disp != nullptr, ns, &smem_bytes, minb);
+  const void *kernel = sweep_kernel<NV, VW, M>(up != 0, disp != nullptr, ns, &smem_bytes, minb);
   if (kernel == nullptr) return 1;
   Params P;
   P.cost = cost; P.out = out; P.extra = extra; P.extra2 = extra2; P.disp = disp;
@@ -965,26 +978,37 @@ extern "C" __attribute__((visibility("default"))) int stm_debug_vsweep_stats(uns
   return cudaMemcpyToSymbol(vsweep::g_stats, zero, sizeof(zero)) == cudaSuccess ? 0 : -1;
 }
 
-static bool vsweep_lane_map(int D) {
-  const LaneMap m = pick_lane_map(D);
-  // VW == 1: D <= 32, and 64 < D <= 96 / 128 < D <= 160 (D = 96 and 160 are common search ranges)
-  return (m.VW == 4 && m.NV <= 2) || (m.VW == 2 && (m.NV == 1 || m.NV == 3)) ||
-         (m.VW == 1 && (m.NV == 1 || m.NV == 3 || m.NV == 5));
+// The lane map the sweeps run a disparity range with (not always pick_lane_map's: a range that is a
+// multiple of 4 but not of 128 takes the 4-wide map of the next 128 with its last lanes masked --
+// D = 96 or 100 run as D = 128 does, where three or four scalar vectors per lane cost 10-100 % more).
+struct VsMap { int NV, VW; bool masked, ok; };
+static VsMap vsweep_map(int D) {
+  VsMap m{0, 0, false, true};
+  if (D >= 1 && D <= 32) { m.NV = 1; m.VW = 1; }
+  else if (D == 64) { m.NV = 1; m.VW = 2; }
+  else if (D < 64 && D % 2 == 0) { m.NV = 1; m.VW = 2; m.masked = true; }
+  else if (D == 128 || D == 256) { m.NV = D / 128; m.VW = 4; }
+  else if (D < 128 && D % 4 == 0) { m.NV = 1; m.VW = 4; m.masked = true; }
+  else if (D == 192) { m.NV = 3; m.VW = 2; }
+  else if (D > 64 && D <= 96) { m.NV = 3; m.VW = 1; }
+  else if (D > 128 && D <= 160) { m.NV = 5; m.VW = 1; }
+  else m.ok = false;
+  return m;
 }
+static bool vsweep_lane_map(int D) { return vsweep_map(D).ok; }
+static size_t vsweep_dpad(int D) { const VsMap m = vsweep_map(D); return (size_t)m.NV * 32 * m.VW; }
 
 // [imported-row counters][CTA->CTA rings][penalties of both sweeps]
 size_t sgm_vsweep_workspace_bytes(int H, int W, int D) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return 0;
-  const LaneMap m = pick_lane_map(D);
-  return vsweep::flags_and_rings_bytes((size_t)m.NV * 32 * m.VW) + (size_t)2 * H * W * sizeof(float4);
+  return vsweep::flags_and_rings_bytes(vsweep_dpad(D)) + (size_t)2 * H * W * sizeof(float4);
 }
 
 // Once per aggregation, before the two sweeps: the adaptive penalties of both (stream order).
 int launch_sgm_vsweep_prepare(const float *image, int H, int W, int D, float p1, float p2,
                               void *workspace, cudaStream_t stream) {
-  const LaneMap m = pick_lane_map(D);
   float4 *pen = reinterpret_cast<float4 *>(static_cast<char *>(workspace) +
-                                           vsweep::flags_and_rings_bytes((size_t)m.NV * 32 * m.VW));
+                                           vsweep::flags_and_rings_bytes(vsweep_dpad(D)));
   const int n = H * W;
   vsweep::sgm_vsweep_penalties<<<(n + 255) / 256, 256, 0, stream>>>(image, pen, H, W, p1, p2);
   return check_launch("sgm_vsweep_penalties");
@@ -996,12 +1020,13 @@ int sgm_sweep_aborted(unsigned *info3) { return vsweep::take_sweep_abort(info3);
 // Whether launch_sgm_vsweep will take this shape on the current device.
 bool sgm_vsweep_can_run(int H, int W, int D, int variant_group) {
   if (H < 2 || W < 2 || !vsweep_lane_map(D)) return false;
-  const LaneMap m = pick_lane_map(D);
+  const VsMap m = vsweep_map(D);
   int minb = 1;
-#define STM_VSWEEP_CASE(NV_, VW_) \
-  if (m.NV == NV_ && m.VW == VW_) return vsweep::ctas<NV_, VW_>(W, variant_group, &minb) > 0;
-  STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
-  STM_VSWEEP_CASE(1, 1) STM_VSWEEP_CASE(3, 1) STM_VSWEEP_CASE(5, 1)
+#define STM_VSWEEP_CASE(NV_, VW_, M_) \
+  if (m.NV == NV_ && m.VW == VW_ && m.masked == M_) return vsweep::ctas<NV_, VW_, M_>(W, variant_group, &minb) > 0;
+  STM_VSWEEP_CASE(1, 4, false) STM_VSWEEP_CASE(2, 4, false) STM_VSWEEP_CASE(1, 2, false) STM_VSWEEP_CASE(3, 2, false)
+  STM_VSWEEP_CASE(1, 1, false) STM_VSWEEP_CASE(3, 1, false) STM_VSWEEP_CASE(5, 1, false)
+  STM_VSWEEP_CASE(1, 4, true) STM_VSWEEP_CASE(1, 2, true)
 #undef STM_VSWEEP_CASE
   return false;
 }
@@ -1022,14 +1047,15 @@ int launch_sgm_vsweep(const float *cost, const float *image, float *out, const f
   if (volume_streams < 1 || volume_streams > 4 || (volume_streams >= 3) != (extra != nullptr) ||
       (volume_streams == 4) != (extra2 != nullptr))
     return 1;
-  const LaneMap m = pick_lane_map(D);
+  const VsMap m = vsweep_map(D);
   char *ws = static_cast<char *>(workspace);
-#define STM_VSWEEP_CASE(NV_, VW_)      \
-  if (m.NV == NV_ && m.VW == VW_)      \
-    return vsweep::run<NV_, VW_>(cost, image, out, extra, extra2, disp, H, W, D, p1, p2, min_limit, up, store_vol, \
-                                 volume_streams, ws, stream);
-  STM_VSWEEP_CASE(1, 4) STM_VSWEEP_CASE(2, 4) STM_VSWEEP_CASE(1, 2) STM_VSWEEP_CASE(3, 2)
-  STM_VSWEEP_CASE(1, 1) STM_VSWEEP_CASE(3, 1) STM_VSWEEP_CASE(5, 1)
+#define STM_VSWEEP_CASE(NV_, VW_, M_)                             \
+  if (m.NV == NV_ && m.VW == VW_ && m.masked == M_)               \
+    return vsweep::run<NV_, VW_, M_>(cost, image, out, extra, extra2, disp, H, W, D, p1, p2, min_limit, up, store_vol, \
+                                     volume_streams, ws, stream);
+  STM_VSWEEP_CASE(1, 4, false) STM_VSWEEP_CASE(2, 4, false) STM_VSWEEP_CASE(1, 2, false) STM_VSWEEP_CASE(3, 2, false)
+  STM_VSWEEP_CASE(1, 1, false) STM_VSWEEP_CASE(3, 1, false) STM_VSWEEP_CASE(5, 1, false)
+  STM_VSWEEP_CASE(1, 4, true) STM_VSWEEP_CASE(1, 2, true)
 #undef STM_VSWEEP_CASE
   return 1;
 }

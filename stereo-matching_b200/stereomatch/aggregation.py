@@ -34,8 +34,9 @@ class Semiglobal:
         (default) uses them for volumes above 48 MB where a cost model of both schedules says
         they are faster (about W*D >= 600*128, more for D > 128 and for few rows), True always,
         False never (reference order).
-        Shapes the sweeps do not handle (more than 13 columns per SM -- 26 at D <= 64 --, D not
-        in {<= 32, 64, 65..96, 128, 129..160, 192, 256}) take the per-direction passes.
+        Shapes the sweeps do not handle (more than 13 columns per SM -- 26 at D <= 64 --; D above
+        160 other than 192 and 256, odd D between 33 and 63, D between 97 and 127 that is not a
+        multiple of 4) take the per-direction passes.
       * overlap (with the fused sweeps; default on): the two horizontal passes run on a helper
         stream next to the down sweep, which writes a workspace volume of its own that the up
         sweep adds (STM_SGM_OVERLAP).  Costs one more volume of workspace (1.06 GB at 1080p

@@ -40,14 +40,16 @@ def test_workspace_query_is_pure():
     lib = ctypes.CDLL(str(LIB))
     lib.stm_sgm_workspace_bytes.restype = ctypes.c_size_t
 
-    def expect(H, W, dpad):
+    def expect(H, W, dpad, sweep_dpad=None):
         # max of csrc/sgm.cu (one path's vectors for the corner-diagonal replay) and
         # csrc/sgm_vsweep.cu (320 imported-row counters of 128 B + 320 CTA->CTA rings of
-        # 16 rows x 3 vectors of 8-byte (value, tag) words; only for the lane maps it handles)
+        # 16 rows x 3 vectors of 8-byte (value, tag) words; only for the lane maps it handles).
+        # sweep_dpad: the sweeps run ranges that are a multiple of 4 below 128 on the masked 4-wide map
         direction = min(H, W) * dpad * 4
+        sd = dpad if sweep_dpad is None else sweep_dpad
         # + the adaptive penalties of both sweeps, one float4 per pixel each
-        sweeps = (40960 + 320 * 16 * 3 * dpad * 8 + 2 * H * W * 16
-                  if (H >= 2 and W >= 2 and dpad in (32, 64, 96, 128, 160, 192, 256)) else 0)
+        sweeps = (40960 + 320 * 16 * 3 * sd * 8 + 2 * H * W * 16
+                  if (H >= 2 and W >= 2 and sd in (32, 64, 96, 128, 160, 192, 256)) else 0)
         return max(direction, sweeps)
 
     assert lib.stm_sgm_workspace_bytes(1080, 1920, 128) == expect(1080, 1920, 128)
@@ -78,7 +80,8 @@ def test_workspace_query_is_pure():
         assert lib.stm_sgm_workspace_bytes_flags(H, W, D, 1 | 4) == base
     # D = 224 is not a lane map of the sweeps: the flag does not change what the call needs
     assert lib.stm_sgm_workspace_bytes_flags(400, 900, 224, 1 | 4) == a256(expect(400, 900, 224)) + 8 * 400 * 900 * 224 * 4
-    assert lib.stm_sgm_workspace_bytes_flags(540, 960, 96, 1 | 4) == expect(540, 960, 96)   # D = 96: the sweeps run
+    assert lib.stm_sgm_workspace_bytes_flags(540, 960, 96, 1 | 4) == expect(540, 960, 96, 128)   # D = 96: the sweeps run (masked 4-wide map)
+    assert lib.stm_sgm_workspace_bytes_flags(540, 960, 100, 1 | 4) == expect(540, 960, 128, 128)
     assert lib.stm_sgm_workspace_bytes_flags(1080, 1920, 64, 1) == expect(1080, 1920, 64)   # 531 MB: sequential
 
 

@@ -169,7 +169,10 @@ def test_sgm_horizontal_bulk_copy_kernel_tiles(sm, H, W, D):
                                      (20, 3840, 64), (9, 2500, 32), (7, 3848, 48), (6, 3850, 64),
                                      # D = 96 / 160 and ranges below them (three / five scalar vectors per lane)
                                      (60, 200, 96), (150, 70, 96), (40, 1920, 96), (33, 100, 80), (45, 333, 160),
-                                     (20, 301, 150), (64, 64, 96)])
+                                     (20, 301, 150), (64, 64, 96),
+                                     # masked vector maps: multiples of 4 below 128 (4-wide), even ranges below 64 (2-wide)
+                                     (33, 100, 100), (40, 300, 112), (31, 77, 72), (20, 200, 48), (25, 90, 40),
+                                     (12, 1920, 100), (90, 60, 120), (30, 50, 36)])
 def test_sgm_sweeps_many_ctas_and_ring_wraps(sm, H, W, D):
     """Fused vertical sweeps (csrc/sgm_vsweep.cu): one CTA to 148 CTAs, 2 to 13 column slots
     per CTA, more rows than every hand-off ring (4 rows in shared memory, 16 in global memory),
@@ -601,7 +604,7 @@ def test_full_size_1080p_properties(sm):
 
 
 @pytest.mark.parametrize("H,W,D", [(30, 47, 128), (47, 30, 64), (21, 21, 32), (19, 333, 192), (30, 47, 96),
-                                   (19, 333, 160), (25, 90, 70)])
+                                   (19, 333, 160), (25, 90, 70), (25, 90, 100), (47, 30, 48)])
 def test_sgm_fused_sweeps_fold_winner_takes_all(sm, H, W, D):
     """stm_sgm_wta_f32 with STM_SGM_FUSED_SWEEPS: the up sweep emits the disparity map; it is
     exactly WinnerTakesAll of the volume the same call returns, the volume meets the oracle
