@@ -85,13 +85,18 @@ struct Cfg {
 
 }  // namespace rowk
 
-template <int NV, int VW, bool ACC, bool BACKWARD>
+// MASKED (NV == 1): the range D_real is a multiple of 4 below the padded 32 * VW; a pixel's vector is
+// D_real floats in memory and in the tiles, the lanes beyond it hold +inf and neither load nor store
+// (D = 100 or 112 then take this kernel instead of the scalar-lane path kernel).
+template <int NV, int VW, bool ACC, bool BACKWARD, bool MASKED = false>
 __global__ void __launch_bounds__(rowk::kWarps * 32)
 sgm_row_kernel(const float *__restrict__ cost, const float *__restrict__ image,
-               float *__restrict__ out, int H, int W, float p1, float p2, int min_limit) {
+               float *__restrict__ out, int H, int W, float p1, float p2, int min_limit, int D_real) {
   using namespace rowk;
   using C = Cfg<NV, VW>;
-  constexpr int TILE = C::kTile, TF = C::kTileFloats, D = C::kDpad;  // host guarantees D == dpad
+  static_assert(!MASKED || NV == 1, "masked maps have one vector per lane");
+  constexpr int TILE = C::kTile, TF = C::kTileFloats;
+  const int D = MASKED ? D_real : C::kDpad;  // not masked: the host guarantees D == dpad
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
   const int y = blockIdx.x * kWarps + wi;
@@ -161,22 +166,30 @@ sgm_row_kernel(const float *__restrict__ cost, const float *__restrict__ image,
 
     auto step = [&](int u, int um) {  // u: traversal index in the tile, um: memory index
       LaneVec<NV, VW> c;
-      lv_load<NV, VW, false>(c, cb + um * D, lane, D);
+      const bool held = !MASKED || lane * VW < D;   // this lane's vector exists
+      if (held) {
+        lv_load<NV, VW, false>(c, cb + um * D, lane, C::kDpad);
+      } else {
+#pragma unroll
+        for (int j = 0; j < VW; ++j) c.v[0][j] = CUDART_INF_F;
+      }
       if (t == 0 && u == 0) {
         L = c;  // first pixel of the path: L = C
       } else {
         lv_sgm_step<NV, VW>(L, c, p1, __shfl_sync(FULL, p2_tile, u), cx);
       }
       if (ACC) {
-        LaneVec<NV, VW> o;
-        lv_load<NV, VW, false>(o, sb + um * D, lane, D);
+        if (held) {
+          LaneVec<NV, VW> o;
+          lv_load<NV, VW, false>(o, sb + um * D, lane, C::kDpad);
 #pragma unroll
-        for (int k = 0; k < NV; ++k)
+          for (int k = 0; k < NV; ++k)
 #pragma unroll
-          for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
-        lv_store<NV, VW, false>(o, sb + um * D, lane, D);
-      } else {
-        lv_store<NV, VW, false>(L, sb + um * D, lane, D);
+            for (int j = 0; j < VW; ++j) o.v[k][j] = __fadd_rn(o.v[k][j], L.v[k][j]);
+          lv_store<NV, VW, false>(o, sb + um * D, lane, C::kDpad);
+        }
+      } else if (held) {
+        lv_store<NV, VW, false>(L, sb + um * D, lane, C::kDpad);
       }
     };
     if (np == TILE) {
@@ -202,11 +215,11 @@ sgm_row_kernel(const float *__restrict__ cost, const float *__restrict__ image,
   if (lane == 0) bulk_wait_all();  // shared memory must outlive the last stores
 }
 
-template <int NV, int VW>
+template <int NV, int VW, bool MASKED = false>
 static int run_sgm_row(const float *cost, const float *image, float *out, int H, int W, int D,
                        float p1, float p2, int dir, int min_limit, bool acc, cudaStream_t stream) {
   using C = rowk::Cfg<NV, VW>;
-  if (C::kDpad != D) return 1;  // padded lane maps (D % 32 != 0) stay on the generic kernel
+  if (MASKED ? (D >= C::kDpad || D % 4 != 0) : C::kDpad != D) return 1;  // other ranges stay on the generic kernel
   static PerDeviceInt configured;  // the > 48 KB opt-in is per function AND per device
   const int dev = device_slot();
   int done = 0;
@@ -214,7 +227,7 @@ static int run_sgm_row(const float *cost, const float *image, float *out, int H,
     cudaError_t e = cudaSuccess;
 #define STM_ROW_ATTR(A_, B_)                                                                  \
   if (e == cudaSuccess)                                                                      \
-    e = cudaFuncSetAttribute(sgm_row_kernel<NV, VW, A_, B_>,                                 \
+    e = cudaFuncSetAttribute(sgm_row_kernel<NV, VW, A_, B_, MASKED>,                         \
                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::kSmemBytes);
     STM_ROW_ATTR(false, false) STM_ROW_ATTR(false, true) STM_ROW_ATTR(true, false)
     STM_ROW_ATTR(true, true)
@@ -230,13 +243,13 @@ static int run_sgm_row(const float *cost, const float *image, float *out, int H,
   const size_t smem = C::kSmemBytes;
   const bool backward = dir == 1;
   if (acc && backward)
-    sgm_row_kernel<NV, VW, true, true><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit);
+    sgm_row_kernel<NV, VW, true, true, MASKED><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit, D);
   else if (acc)
-    sgm_row_kernel<NV, VW, true, false><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit);
+    sgm_row_kernel<NV, VW, true, false, MASKED><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit, D);
   else if (backward)
-    sgm_row_kernel<NV, VW, false, true><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit);
+    sgm_row_kernel<NV, VW, false, true, MASKED><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit, D);
   else
-    sgm_row_kernel<NV, VW, false, false><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit);
+    sgm_row_kernel<NV, VW, false, false, MASKED><<<grid, block, smem, stream>>>(cost, image, out, H, W, p1, p2, min_limit, D);
   return check_launch("sgm_row_kernel");
 }
 
@@ -245,7 +258,15 @@ static int run_sgm_row(const float *cost, const float *image, float *out, int H,
 int launch_sgm_row(const float *cost, const float *image, float *out, int H, int W, int D,
                    float p1, float p2, int dir, int min_limit, bool acc, cudaStream_t stream) {
   if (dir != 0 && dir != 1) return 1;
-  if (D % 32 != 0 || W < 2) return 1;
+  if (W < 2) return 1;
+  if (D % 32 != 0) {
+    // a multiple of 4 between 32 and 128: the 4-wide map of D = 128, last lanes masked
+    if (D % 4 != 0 || D < 36 || D > 124) return 1;
+    if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out)) & 15) return 1;
+    static const char *off = getenv("STM_DEBUG_SGM_ROW");
+    if (off && off[0] == '0') return 1;
+    return run_sgm_row<1, 4, true>(cost, image, out, H, W, D, p1, p2, dir, min_limit, acc, stream);
+  }
   if ((reinterpret_cast<uintptr_t>(cost) | reinterpret_cast<uintptr_t>(out)) & 15) return 1;  // bulk copies
   {
     static const char *off = getenv("STM_DEBUG_SGM_ROW");  // developer knob: "0" disables
