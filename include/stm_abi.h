@@ -111,7 +111,7 @@ int stm_birchfield_f32(const float *left, const float *right, float *cost, int H
  * stereomatch/pipeline.py:80-92 chains compute_birchfield, src/cost.cpp:14, and
  * run_winners_take_all, src/disparity_reduce.cpp:6-9).  The disparity map is exactly stm_wta_f32 of
  * stm_birchfield_f32's volume (tested); HBM traffic is 4 bytes per PIXEL (the map) instead of 8 bytes
- * per pixel-disparity (volume written, then read).  D % 64 == 0 only; other shapes return STM_EUNSUPPORTED
+ * per pixel-disparity (volume written, then read).  D % 32 == 0 (up to 256) only; other shapes return STM_EUNSUPPORTED
  * (the binding then runs the two stages).  New, SURVEY.md 8(f) N1. */
 int stm_birchfield_wta_f32(const float *left, const float *right, int32_t *disparity, int H, int W,
                            int D, void *stream);

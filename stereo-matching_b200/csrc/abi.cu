@@ -113,7 +113,7 @@ int stm_birchfield_wta_f32(const float *left, const float *right, int32_t *dispa
   if ((rc = require_device())) return rc;
   rc = launch_birchfield_wta(left, right, disparity, H, W, D, (cudaStream_t)stream);
   if (rc == 1)
-    return fail(STM_EUNSUPPORTED, "birchfield_wta: needs D %% 64 == 0 and 8 <= W <= ~6000 (got W=%d D=%d); "
+    return fail(STM_EUNSUPPORTED, "birchfield_wta: needs D %% 32 == 0 (64..256) and 8 <= W <= ~6000 (got W=%d D=%d); "
                 "use stm_birchfield_f32 + stm_wta_f32", W, D);
   return rc;
 }

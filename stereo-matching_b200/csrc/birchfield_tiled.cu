@@ -148,13 +148,17 @@ __device__ __forceinline__ u64 add2(u64 a, u64 b) {
 // wins, NaN at d = 0 -> 0, the rule of wta.cu / reference src/winners_take_all.cu:21-40 -- and writes
 // 4 bytes per pixel instead of 4 bytes per pixel-disparity (cost + reduce of a
 // pipeline without aggregation in one kernel).
-template <int NJ, bool WTA>
+// ODD: the range is 32 * (NJ - 1) -- 96, 160, 224: the pairs are formed as for 32 * NJ and the last
+// group of 32 disparities is computed but neither stored nor offered to the argmin (a quarter more
+// arithmetic at D = 96 than needed, still a third faster than the unpacked kernel those ranges took).
+template <int NJ, bool WTA, bool ODD = false>
 __global__ void __launch_bounds__(256)
 birchfield_row_packed_kernel(const float *__restrict__ left, const float *__restrict__ right,
                              float *__restrict__ cost, int32_t *__restrict__ disp, int H, int W, int part_w) {
   using namespace bt2;
   static_assert(NJ % 2 == 0, "disparity groups are processed in pairs");
   constexpr int D = 32 * NJ, NP = NJ / 2;
+  constexpr int DR = ODD ? D - 32 : D;   // the range in memory
   extern __shared__ float4 smq[];
   float4 *sLq = smq;               // [W + 8]:      pixel p at index p + 4,      p in [-4, W + 3]
   float4 *sRq = smq + (W + 8);     // [W + D + 8]:  pixel q at index q + D + 4,  q in [-D - 4, W + 3]
@@ -209,7 +213,7 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
 #pragma unroll
   for (int k = 0; k < 7; ++k) eval(xa - 4 + k, win[(k + 4) & 7]);
 
-  float *orow = WTA ? nullptr : cost + ((size_t)y * W + xa) * D + lane;
+  float *orow = WTA ? nullptr : cost + ((size_t)y * W + xa) * DR + lane;
   int32_t *drow = WTA ? disp + (size_t)y * W : nullptr;
   auto block8 = [&](auto edge_tag, auto tail_tag, int x0) {
     constexpr bool EDGE = decltype(edge_tag)::value, TAIL = decltype(tail_tag)::value;
@@ -234,13 +238,13 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
             if (lane + 64 * q + 32 > x) s1 = CUDART_INF_F;
           }
           if constexpr (!WTA) {
-            __stcs(orow + u * D + 64 * q, s0);
-            __stcs(orow + u * D + 64 * q + 32, s1);
+            __stcs(orow + u * DR + 64 * q, s0);
+            if (!(ODD && q == NP - 1)) __stcs(orow + u * DR + 64 * q + 32, s1);
           } else {
             // ascending d within the lane, strict <: the lowest d of equal values sticks; NaN never passes
             if (q == 0) nan_at_0 = s0 != s0;
             if (s0 < best) { best = s0; best_d = lane + 64 * q; }
-            if (s1 < best) { best = s1; best_d = lane + 64 * q + 32; }
+            if (!(ODD && q == NP - 1) && s1 < best) { best = s1; best_d = lane + 64 * q + 32; }
           }
         }
         if constexpr (WTA) {
@@ -257,7 +261,7 @@ birchfield_row_packed_kernel(const float *__restrict__ left, const float *__rest
     if constexpr (WTA) {
       if (lane < 8 && x0 + lane < xb) drow[x0 + lane] = mine;
     } else {
-      orow += 8 * D;
+      orow += 8 * DR;
     }
   };
   int x0 = xa;
@@ -280,11 +284,11 @@ static int bt_parts(int H, int W) {
   return (idle(H) > 0.06 && idle(2 * H) < idle(H) - 0.03) ? 2 : 1;
 }
 
-template <int NJ, bool WTA>
+template <int NJ, bool WTA, bool ODD = false>
 static int run_birchfield_packed(const float *left, const float *right, float *cost, int32_t *disp, int H,
                                  int W, cudaStream_t stream) {
   const size_t smem = (size_t)(2 * W + 32 * NJ + 16) * sizeof(float4);
-  auto kernel = birchfield_row_packed_kernel<NJ, WTA>;
+  auto kernel = birchfield_row_packed_kernel<NJ, WTA, ODD>;
   if (smem > 48 * 1024)  // per device and cheap: set on every call (stm_common.cuh, per-device state)
     STM_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int parts = bt_parts(H, W);
@@ -303,11 +307,14 @@ static int run_birchfield_packed(const float *left, const float *right, float *c
 // Birchfield cost + winner-takes-all without the volume.  Returns 1 when the shape is not handled.
 int launch_birchfield_wta(const float *left, const float *right, int32_t *disp, int H, int W, int D,
                           cudaStream_t stream) {
-  if (D % 64 != 0 || W < 8 || (size_t)(2 * W + D + 16) * sizeof(float4) > 200 * 1024) return 1;
+  if (D % 32 != 0 || W < 8 || (size_t)(2 * W + D + 48) * sizeof(float4) > 200 * 1024) return 1;
   switch (D / 32) {
     case 2: return run_birchfield_packed<2, true>(left, right, nullptr, disp, H, W, stream);
+    case 3: return run_birchfield_packed<4, true, true>(left, right, nullptr, disp, H, W, stream);
     case 4: return run_birchfield_packed<4, true>(left, right, nullptr, disp, H, W, stream);
+    case 5: return run_birchfield_packed<6, true, true>(left, right, nullptr, disp, H, W, stream);
     case 6: return run_birchfield_packed<6, true>(left, right, nullptr, disp, H, W, stream);
+    case 7: return run_birchfield_packed<8, true, true>(left, right, nullptr, disp, H, W, stream);
     case 8: return run_birchfield_packed<8, true>(left, right, nullptr, disp, H, W, stream);
     default: return 1;
   }
@@ -328,13 +335,16 @@ static int run_birchfield_tiled(const float *left, const float *right, float *co
 int launch_birchfield_tiled(const float *left, const float *right, float *cost, int H, int W, int D,
                             cudaStream_t stream) {
   if ((size_t)6 * W * sizeof(float) > 200 * 1024 || W < 8) return 1;
-  if (D % 64 == 0 && (size_t)(2 * W + D + 16) * sizeof(float4) <= 200 * 1024 &&
+  if (D % 32 == 0 && (size_t)(2 * W + D + 48) * sizeof(float4) <= 200 * 1024 &&
       !((reinterpret_cast<uintptr_t>(cost)) & 3)) {
     static const char *off = getenv("STM_DEBUG_BT_PACKED");  // developer knob: "0" = kernel above
     if (!(off && off[0] == '0')) switch (D / 32) {
       case 2: return run_birchfield_packed<2, false>(left, right, cost, nullptr, H, W, stream);
+      case 3: return run_birchfield_packed<4, false, true>(left, right, cost, nullptr, H, W, stream);
       case 4: return run_birchfield_packed<4, false>(left, right, cost, nullptr, H, W, stream);
+      case 5: return run_birchfield_packed<6, false, true>(left, right, cost, nullptr, H, W, stream);
       case 6: return run_birchfield_packed<6, false>(left, right, cost, nullptr, H, W, stream);
+      case 7: return run_birchfield_packed<8, false, true>(left, right, cost, nullptr, H, W, stream);
       case 8: return run_birchfield_packed<8, false>(left, right, cost, nullptr, H, W, stream);
       default: break;
     }

@@ -326,7 +326,7 @@ class CostOps:
     def compute_birchfield_wta(left_image, right_image, disparity_image, max_disparity: int) -> bool:
         """New: compute_birchfield + run_winners_take_all in one kernel, the volume never written
         (include/stm_abi.h, stm_birchfield_wta_f32).  Returns False when the shape is not supported
-        (D % 64 != 0 ...): the caller then runs the two stages."""
+        (D % 32 != 0 ...): the caller then runs the two stages."""
         left = _gpu("BirchfieldKernel: left_image", left_image, torch.float32, 2)
         right = _gpu("BirchfieldKernel: right_image", right_image, torch.float32, 2, left)
         disp = _out("disparity_image",

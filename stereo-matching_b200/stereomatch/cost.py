@@ -92,7 +92,7 @@ class Birchfield:
         """New: Birchfield cost followed by winner-takes-all in one kernel; the cost volume is never
         written (4 bytes of HBM traffic per pixel instead of 8 per pixel-disparity).  Returns the
         int32 disparity map -- exactly WinnerTakesAll()(self(left, right)) -- or None when the shape
-        is not supported (max_disparity % 64 != 0), in which case the caller runs the two stages."""
+        is not supported (max_disparity % 32 != 0), in which case the caller runs the two stages."""
         disparity_img = empty_tensor(left_image.size(0), left_image.size(1), dtype=torch.int32,
                                      device=left_image.device, reuse_tensor=disparity_img)
         ok = _CostOps.compute_birchfield_wta(left_image.float(), right_image.float(), disparity_img,
